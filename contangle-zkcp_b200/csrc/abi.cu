@@ -1,0 +1,387 @@
+// C ABI of libctg_groth16.so (include/ctg_groth16.h): context management, host<->device
+// staging and argument checking around the kernels in ntt.cu / msm*.cu / prove.cu / fields.cu.
+// No CPU fallback exists anywhere below this file: every compute entry point launches CUDA
+// kernels on the context's device or fails with an error code.
+#include <cstring>
+
+#include "ctg_internal.h"
+
+struct ctg_pk;
+struct ctg_r1cs;
+
+namespace ctg {
+int32_t field_op_dev(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n, cudaStream_t st);
+size_t field_elem_bytes(int field);
+int32_t imad_probe(ctg_ctx* ctx, double* imad_per_s, double* fq_mul_per_s);
+int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, ctg_pk** out);
+void pk_free(ctg_pk* pk);
+int32_t r1cs_upload(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, const ctg_csr* const mats[3], ctg_r1cs** out);
+void r1cs_free(ctg_r1cs* r);
+int32_t witness_map_host(ctg_ctx* ctx, const ctg_r1cs* r, const ctg_fr* z, ctg_fr* h_out);
+int32_t prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out, ctg_timings* tm);
+uint64_t pk_num_vars(const ctg_pk* pk);
+
+int32_t fail(ctg_ctx* ctx, int32_t code, const std::string& msg) {
+  if (ctx) ctx->last_error = msg;
+  return code;
+}
+int32_t ensure_scratch(ctg_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->scratch_bytes) return CTG_OK;
+  if (ctx->scratch) {
+    CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->scratch);
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+  }
+  size_t want = bytes + bytes / 8 + 4096;
+  cudaError_t e = cudaMalloc(&ctx->scratch, want);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, CTG_ERR_OOM, "out of device memory for scratch"); }
+  ctx->scratch_bytes = want;
+  return CTG_OK;
+}
+int32_t ensure_pinned(ctg_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->pinned_bytes) return CTG_OK;
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  ctx->pinned = nullptr;
+  ctx->pinned_bytes = 0;
+  CTG_CUDA(ctx, cudaMallocHost(&ctx->pinned, bytes));
+  ctx->pinned_bytes = bytes;
+  return CTG_OK;
+}
+static ctg_timings g_last_timings;  // per process is enough: one in-flight call per context
+}  // namespace ctg
+
+using namespace ctg;
+
+static thread_local std::string g_null_ctx_error = "null context";
+
+static int32_t msm_check(ctg_ctx* ctx, const ctg_bases* bases, int group, uint64_t n) {
+  if (!ctx) return CTG_ERR_INVALID;
+  if (!bases) return fail(ctx, CTG_ERR_INVALID, "msm: null bases");
+  if (bases->b.group != group) return fail(ctx, CTG_ERR_INVALID, "msm: base table is for the other group");
+  if (n > bases->b.n) return fail(ctx, CTG_ERR_INVALID, "msm: more scalars than bases");
+  return CTG_OK;
+}
+template <class XY, class AF>
+static int32_t msm_host(ctg_ctx* ctx, const ctg_bases* bases, int group, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, void* out_affine,
+                        void* out_xyzz) {
+  CTG_TRY(msm_check(ctx, bases, group, n));
+  if (n && !host_scalars) return fail(ctx, CTG_ERR_INVALID, "msm: null scalars");
+  const size_t sb = n * sizeof(Fr);
+  CTG_TRY(ensure_scratch(ctx, sb + sizeof(XY) + sizeof(AF) + 128));
+  char* d = (char*)ctx->scratch;
+  XY* d_res = (XY*)(d + ((sb + 63) & ~(size_t)63));
+  AF* d_aff = (AF*)(d_res + 1);
+  if (n) CTG_CUDA(ctx, cudaMemcpyAsync(d, host_scalars, sb, cudaMemcpyHostToDevice, ctx->stream));
+  if (group == 1) CTG_TRY(ctg_msm_g1_dev(ctx, bases, d, n, flags, d_res));
+  else CTG_TRY(ctg_msm_g2_dev(ctx, bases, d, n, flags, d_res));
+  if (out_xyzz) CTG_CUDA(ctx, cudaMemcpyAsync(out_xyzz, d_res, sizeof(XY), cudaMemcpyDeviceToHost, ctx->stream));
+  if (out_affine) {
+    if (group == 1) CTG_TRY(g1_to_affine_dev(ctx, (const G1XYZZ*)d_res, (G1Affine*)d_aff, 1, ctx->stream));
+    else CTG_TRY(g2_to_affine_dev(ctx, (const G2XYZZ*)d_res, (G2Affine*)d_aff, 1, ctx->stream));
+    CTG_CUDA(ctx, cudaMemcpyAsync(out_affine, d_aff, sizeof(AF), cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+
+extern "C" {
+
+int32_t ctg_ctx_create(const int* device_ids, int n_devices, ctg_ctx** out) {
+  if (!out) return CTG_ERR_INVALID;
+  *out = nullptr;
+  if (n_devices != 1 || !device_ids) return CTG_ERR_INVALID;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return CTG_ERR_CUDA;  // no device: no fallback
+  if (device_ids[0] < 0 || device_ids[0] >= count) return CTG_ERR_INVALID;
+  if (cudaSetDevice(device_ids[0]) != cudaSuccess) return CTG_ERR_CUDA;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device_ids[0]) != cudaSuccess) return CTG_ERR_CUDA;
+  if (prop.major != 10) return CTG_ERR_STATE;  // kernels are built for sm_100a only
+  ctg_ctx* ctx = new ctg_ctx();
+  ctx->device = device_ids[0];
+  ctx->sm_count = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return CTG_ERR_CUDA; }
+  ctx->own_stream = true;
+  *out = ctx;
+  return CTG_OK;
+}
+
+void ctg_ctx_destroy(ctg_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto& kv : ctx->domains) {
+    cudaFree(kv.second.tw_fwd); cudaFree(kv.second.tw_inv); cudaFree(kv.second.gpow); cudaFree(kv.second.gpow_n); cudaFree(kv.second.gipow_n);
+  }
+  for (auto& w : ctx->ws) msm_ws_free(w);
+  if (ctx->scratch) cudaFree(ctx->scratch);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->events_ready) for (auto& e : ctx->ev) cudaEventDestroy(e);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char* ctg_last_error(ctg_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_null_ctx_error.c_str(); }
+
+int32_t ctg_ctx_set_stream(ctg_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return CTG_ERR_INVALID;
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  ctx->stream = (cudaStream_t)cuda_stream;
+  ctx->own_stream = false;
+  return CTG_OK;
+}
+int32_t ctg_sync(ctg_ctx* ctx) {
+  if (!ctx) return CTG_ERR_INVALID;
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+uint64_t ctg_launch_count(ctg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int32_t ctg_last_timings(ctg_ctx* ctx, ctg_timings* out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  *out = g_last_timings;
+  return CTG_OK;
+}
+
+int32_t ctg_dev_alloc(ctg_ctx* ctx, size_t bytes, void** d_out) {
+  if (!ctx || !d_out) return CTG_ERR_INVALID;
+  cudaError_t e = cudaMalloc(d_out, bytes ? bytes : 1);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, CTG_ERR_OOM, "cudaMalloc failed"); }
+  return CTG_OK;
+}
+int32_t ctg_dev_free(ctg_ctx* ctx, void* d_ptr) {
+  if (!ctx) return CTG_ERR_INVALID;
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  CTG_CUDA(ctx, cudaFree(d_ptr));
+  return CTG_OK;
+}
+int32_t ctg_h2d(ctg_ctx* ctx, void* d_dst, const void* h_src, size_t bytes) {
+  if (!ctx) return CTG_ERR_INVALID;
+  CTG_CUDA(ctx, cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+int32_t ctg_d2h(ctg_ctx* ctx, void* h_dst, const void* d_src, size_t bytes) {
+  if (!ctx) return CTG_ERR_INVALID;
+  CTG_CUDA(ctx, cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+
+// ---- fields -----------------------------------------------------------------------------------
+int32_t ctg_field_op_batch(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n) {
+  if (!ctx) return CTG_ERR_INVALID;
+  const size_t eb = field_elem_bytes(field);
+  if (!eb) return fail(ctx, CTG_ERR_INVALID, "unknown field");
+  if (n == 0) return CTG_OK;
+  if (!a || !b || !out) return fail(ctx, CTG_ERR_INVALID, "null buffer");
+  CTG_TRY(ensure_scratch(ctx, 3 * n * eb));
+  char* d = (char*)ctx->scratch;
+  CTG_CUDA(ctx, cudaMemcpyAsync(d, a, n * eb, cudaMemcpyHostToDevice, ctx->stream));
+  CTG_CUDA(ctx, cudaMemcpyAsync(d + n * eb, b, n * eb, cudaMemcpyHostToDevice, ctx->stream));
+  CTG_TRY(field_op_dev(ctx, field, op, d, d + n * eb, d + 2 * n * eb, n, ctx->stream));
+  CTG_CUDA(ctx, cudaMemcpyAsync(out, d + 2 * n * eb, n * eb, cudaMemcpyDeviceToHost, ctx->stream));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+int32_t ctg_fr_mul_batch(ctg_ctx* ctx, const ctg_fr* a, const ctg_fr* b, ctg_fr* out, size_t n) {
+  return ctg_field_op_batch(ctx, CTG_FIELD_FR, CTG_OP_MUL, a, b, out, n);
+}
+int32_t ctg_fq_mul_batch(ctg_ctx* ctx, const ctg_fq* a, const ctg_fq* b, ctg_fq* out, size_t n) {
+  return ctg_field_op_batch(ctx, CTG_FIELD_FQ, CTG_OP_MUL, a, b, out, n);
+}
+int32_t ctg_imad_peak_probe(ctg_ctx* ctx, double* imad_per_s, double* fq_mul_per_s) {
+  if (!ctx) return CTG_ERR_INVALID;
+  return imad_probe(ctx, imad_per_s, fq_mul_per_s);
+}
+
+// ---- NTT --------------------------------------------------------------------------------------
+int32_t ctg_ntt_fr_dev(ctg_ctx* ctx, void* d_data, uint32_t log_n, int inverse, int coset) {
+  if (!ctx || !d_data) return ctx ? fail(ctx, CTG_ERR_INVALID, "ntt: null buffer") : CTG_ERR_INVALID;
+  return ntt_run(ctx, (Fr*)d_data, (int)log_n, inverse, coset, ctx->stream);
+}
+int32_t ctg_ntt_fr(ctg_ctx* ctx, ctg_fr* host_data, uint32_t log_n, int inverse, int coset) {
+  if (!ctx || !host_data) return ctx ? fail(ctx, CTG_ERR_INVALID, "ntt: null buffer") : CTG_ERR_INVALID;
+  if (log_n > 28) return fail(ctx, CTG_ERR_INVALID, "ntt: log_n out of range [0, 28]");
+  const size_t bytes = ((size_t)1 << log_n) * sizeof(Fr);
+  CTG_TRY(ensure_scratch(ctx, bytes));
+  CTG_CUDA(ctx, cudaMemcpyAsync(ctx->scratch, host_data, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CTG_TRY(ntt_run(ctx, (Fr*)ctx->scratch, (int)log_n, inverse, coset, ctx->stream));
+  CTG_CUDA(ctx, cudaMemcpyAsync(host_data, ctx->scratch, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+
+// ---- bases ------------------------------------------------------------------------------------
+static int32_t bases_new(ctg_ctx* ctx, int group, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  if (c_bits != 0 && (c_bits < 2 || c_bits > 16)) return fail(ctx, CTG_ERR_INVALID, "bases: c_bits must be 0 or in [2, 16]");
+  if (copies < 0) return fail(ctx, CTG_ERR_INVALID, "bases: copies must be >= 0");
+  ctg_bases* h = new ctg_bases();
+  h->b.group = group;
+  h->b.n = n;
+  h->b.plan = msm_make_plan(n, copies, c_bits);
+  if (n * (uint64_t)h->b.plan.copies >= (1ull << 31)) { delete h; return fail(ctx, CTG_ERR_INVALID, "bases: n * copies must be < 2^31"); }
+  const size_t eb = group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+  const size_t bytes = (size_t)h->b.plan.copies * (n ? n : 1) * eb;
+  cudaError_t e = cudaMalloc(&h->b.pts, bytes);
+  if (e != cudaSuccess) { cudaGetLastError(); delete h; return fail(ctx, CTG_ERR_OOM, "bases: out of device memory (fewer copies?)"); }
+  *out = h;
+  return CTG_OK;
+}
+static int32_t bases_finish(ctg_ctx* ctx, ctg_bases* h) {
+  int32_t rc = h->b.group == 1 ? g1_precompute(ctx, h->b, ctx->stream) : g2_precompute(ctx, h->b, ctx->stream);
+  if (rc != CTG_OK) return rc;
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return CTG_OK;
+}
+int32_t ctg_bases_upload_g1(ctg_ctx* ctx, const ctg_g1_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  CTG_TRY(bases_new(ctx, 1, n, copies, c_bits, out));
+  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G1Affine), cudaMemcpyHostToDevice, ctx->stream));
+  return bases_finish(ctx, *out);
+}
+int32_t ctg_bases_upload_g2(ctg_ctx* ctx, const ctg_g2_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  CTG_TRY(bases_new(ctx, 2, n, copies, c_bits, out));
+  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G2Affine), cudaMemcpyHostToDevice, ctx->stream));
+  return bases_finish(ctx, *out);
+}
+int32_t ctg_bases_progression_g1(ctg_ctx* ctx, const ctg_g1_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (!g || !a || !b) return ctx ? fail(ctx, CTG_ERR_INVALID, "progression: null argument") : CTG_ERR_INVALID;
+  CTG_TRY(bases_new(ctx, 1, n, copies, c_bits, out));
+  G1Affine gg; Fr fa, fb;
+  memcpy(&gg, g, sizeof(gg)); memcpy(&fa, a, sizeof(fa)); memcpy(&fb, b, sizeof(fb));
+  if (n) CTG_TRY(g1_progression_dev(ctx, gg, fa, fb, n, (G1Affine*)(*out)->b.pts, ctx->stream));
+  return bases_finish(ctx, *out);
+}
+int32_t ctg_bases_progression_g2(ctg_ctx* ctx, const ctg_g2_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (!g || !a || !b) return ctx ? fail(ctx, CTG_ERR_INVALID, "progression: null argument") : CTG_ERR_INVALID;
+  CTG_TRY(bases_new(ctx, 2, n, copies, c_bits, out));
+  G2Affine gg; Fr fa, fb;
+  memcpy(&gg, g, sizeof(gg)); memcpy(&fa, a, sizeof(fa)); memcpy(&fb, b, sizeof(fb));
+  if (n) CTG_TRY(g2_progression_dev(ctx, gg, fa, fb, n, (G2Affine*)(*out)->b.pts, ctx->stream));
+  return bases_finish(ctx, *out);
+}
+int32_t ctg_bases_download(ctg_ctx* ctx, const ctg_bases* bases, uint64_t first, uint64_t count, void* host_points) {
+  if (!ctx || !bases || !host_points) return CTG_ERR_INVALID;
+  const uint64_t total = bases->b.n * (uint64_t)bases->b.plan.copies;
+  if (first + count > total) return fail(ctx, CTG_ERR_INVALID, "bases_download: range out of bounds");
+  const size_t eb = bases->b.group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+  return ctg_d2h(ctx, host_points, (const char*)bases->b.pts + first * eb, count * eb);
+}
+void ctg_bases_free(ctg_ctx* ctx, ctg_bases* bases) {
+  if (!bases) return;
+  if (ctx) cudaStreamSynchronize(ctx->stream);
+  cudaFree(bases->b.pts);
+  delete bases;
+}
+uint64_t ctg_bases_len(const ctg_bases* bases) { return bases ? bases->b.n : 0; }
+
+// ---- MSM --------------------------------------------------------------------------------------
+int32_t ctg_msm_g1_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {
+  CTG_TRY(msm_check(ctx, bases, 1, n));
+  float st[3];
+  int32_t rc = msm_g1_run(ctx, ctx->ws[0], bases->b, (const uint32_t*)d_scalars, n, (flags & CTG_SCALARS_MONT) != 0, (G1XYZZ*)d_out_xyzz, ctx->stream,
+                          (flags & 0x100u) ? st : nullptr);
+  if (rc == CTG_OK && (flags & 0x100u)) { g_last_timings.msm_sort_ms = st[0]; g_last_timings.msm_accumulate_ms = st[1]; g_last_timings.msm_reduce_ms = st[2]; }
+  return rc;
+}
+int32_t ctg_msm_g2_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {
+  CTG_TRY(msm_check(ctx, bases, 2, n));
+  float st[3];
+  int32_t rc = msm_g2_run(ctx, ctx->ws[0], bases->b, (const uint32_t*)d_scalars, n, (flags & CTG_SCALARS_MONT) != 0, (G2XYZZ*)d_out_xyzz, ctx->stream,
+                          (flags & 0x100u) ? st : nullptr);
+  if (rc == CTG_OK && (flags & 0x100u)) { g_last_timings.msm_sort_ms = st[0]; g_last_timings.msm_accumulate_ms = st[1]; g_last_timings.msm_reduce_ms = st[2]; }
+  return rc;
+}
+
+int32_t ctg_msm_g1(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_affine* out) {
+  if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
+  return msm_host<G1XYZZ, G1Affine>(ctx, bases, 1, host_scalars, n, flags, out, nullptr);
+}
+int32_t ctg_msm_g2(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g2_affine* out) {
+  if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
+  return msm_host<G2XYZZ, G2Affine>(ctx, bases, 2, host_scalars, n, flags, out, nullptr);
+}
+int32_t ctg_msm_g1_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_xyzz* out) {
+  if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
+  return msm_host<G1XYZZ, G1Affine>(ctx, bases, 1, host_scalars, n, flags, nullptr, out);
+}
+int32_t ctg_msm_g2_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g2_xyzz* out) {
+  if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
+  return msm_host<G2XYZZ, G2Affine>(ctx, bases, 2, host_scalars, n, flags, nullptr, out);
+}
+
+int32_t ctg_g1_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine) {
+  if (!ctx || !d_partials || !d_out_affine) return CTG_ERR_INVALID;
+  return g1_combine_dev(ctx, (const G1XYZZ*)d_partials, k, (G1Affine*)d_out_affine, nullptr, ctx->stream);
+}
+int32_t ctg_g2_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine) {
+  if (!ctx || !d_partials || !d_out_affine) return CTG_ERR_INVALID;
+  return g2_combine_dev(ctx, (const G2XYZZ*)d_partials, k, (G2Affine*)d_out_affine, nullptr, ctx->stream);
+}
+int32_t ctg_g1_combine(ctg_ctx* ctx, const ctg_g1_xyzz* host_partials, uint32_t k, ctg_g1_affine* out) {
+  if (!ctx || !host_partials || !out) return CTG_ERR_INVALID;
+  CTG_TRY(ensure_scratch(ctx, (size_t)k * sizeof(G1XYZZ) + sizeof(G1Affine) + 64));
+  char* d = (char*)ctx->scratch;
+  G1Affine* d_out = (G1Affine*)(d + (size_t)k * sizeof(G1XYZZ));
+  CTG_CUDA(ctx, cudaMemcpyAsync(d, host_partials, (size_t)k * sizeof(G1XYZZ), cudaMemcpyHostToDevice, ctx->stream));
+  CTG_TRY(g1_combine_dev(ctx, (const G1XYZZ*)d, k, d_out, nullptr, ctx->stream));
+  return ctg_d2h(ctx, out, d_out, sizeof(G1Affine));
+}
+int32_t ctg_g2_combine(ctg_ctx* ctx, const ctg_g2_xyzz* host_partials, uint32_t k, ctg_g2_affine* out) {
+  if (!ctx || !host_partials || !out) return CTG_ERR_INVALID;
+  CTG_TRY(ensure_scratch(ctx, (size_t)k * sizeof(G2XYZZ) + sizeof(G2Affine) + 64));
+  char* d = (char*)ctx->scratch;
+  G2Affine* d_out = (G2Affine*)(d + (size_t)k * sizeof(G2XYZZ));
+  CTG_CUDA(ctx, cudaMemcpyAsync(d, host_partials, (size_t)k * sizeof(G2XYZZ), cudaMemcpyHostToDevice, ctx->stream));
+  CTG_TRY(g2_combine_dev(ctx, (const G2XYZZ*)d, k, d_out, nullptr, ctx->stream));
+  return ctg_d2h(ctx, out, d_out, sizeof(G2Affine));
+}
+
+// ---- proving key / R1CS / prover --------------------------------------------------------------
+int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits, ctg_pk** out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  if (c_bits != 0 && (c_bits < 2 || c_bits > 16)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 16]");
+  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, out);
+}
+void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk) {
+  if (ctx) cudaStreamSynchronize(ctx->stream);
+  pk_free(pk);
+}
+int32_t ctg_r1cs_upload(ctg_ctx* ctx, uint64_t num_instance, uint64_t num_witness, uint64_t num_constraints, const ctg_csr* a, const ctg_csr* b,
+                        const ctg_csr* c, ctg_r1cs** out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  const ctg_csr* mats[3] = {a, b, c};
+  return r1cs_upload(ctx, num_instance, num_witness, num_constraints, mats, out);
+}
+void ctg_r1cs_free(ctg_ctx* ctx, ctg_r1cs* r1cs) {
+  if (ctx) cudaStreamSynchronize(ctx->stream);
+  r1cs_free(r1cs);
+}
+int32_t ctg_witness_map(ctg_ctx* ctx, const ctg_r1cs* r1cs, const ctg_fr* z, ctg_fr* h_out) {
+  if (!ctx || !r1cs || !z || !h_out) return ctx ? fail(ctx, CTG_ERR_INVALID, "witness_map: null argument") : CTG_ERR_INVALID;
+  return witness_map_host(ctx, r1cs, z, h_out);
+}
+int32_t ctg_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s, ctg_proof* out,
+                  ctg_timings* timings) {
+  if (!ctx) return CTG_ERR_INVALID;
+  ctg_timings local;
+  int32_t rc = prove(ctx, pk, r1cs, z, r, s, out, timings ? &local : nullptr);
+  if (rc == CTG_OK && timings) {
+    local.msm_sort_ms = g_last_timings.msm_sort_ms; local.msm_accumulate_ms = g_last_timings.msm_accumulate_ms; local.msm_reduce_ms = g_last_timings.msm_reduce_ms;
+    *timings = local;
+    g_last_timings = local;
+  }
+  return rc;
+}
+int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch,
+                        ctg_proof* out) {
+  if (!ctx || !pk || !r1cs || !z_batch || !rs_batch || !out) return ctx ? fail(ctx, CTG_ERR_INVALID, "prove_batch: null argument") : CTG_ERR_INVALID;
+  const uint64_t m = pk_num_vars(pk);
+  for (uint32_t i = 0; i < n_proofs; i++)
+    CTG_TRY(prove(ctx, pk, r1cs, z_batch + (size_t)i * m, rs_batch + 2 * (size_t)i, rs_batch + 2 * (size_t)i + 1, out + i, nullptr));
+  return CTG_OK;
+}
+
+}  // extern "C"

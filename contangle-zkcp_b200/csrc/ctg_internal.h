@@ -1,0 +1,129 @@
+// Internal host-side declarations shared by the translation units of libctg_groth16.so.
+// Nothing here crosses the C ABI (include/ctg_groth16.h does).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/ctg_groth16.h"
+#include "curve.cuh"
+#include "fp.cuh"
+
+namespace ctg {
+
+struct NttDomain {
+  int log_n = 0;
+  Fr* tw_fwd = nullptr;   // w^k,  k < n/2
+  Fr* tw_inv = nullptr;   // w^-k, k < n/2
+  Fr* gpow = nullptr;     // g^i            (coset_fft premultiplier)
+  Fr* gpow_n = nullptr;   // g^i / n        (ifft followed by coset_fft, fused)
+  Fr* gipow_n = nullptr;  // g^-i / n       (coset_ifft postmultiplier)
+  Fr n_inv;               // 1/n (Montgomery)
+  Fr zinv;                // 1/(g^n - 1)
+};
+
+// Per-MSM scratch.  One instance per concurrently running MSM.
+struct MsmWorkspace {
+  uint32_t* counts = nullptr;   // [nb + 1] bucket sizes, then exclusive starts
+  uint32_t* cursor = nullptr;   // [nb]
+  uint32_t* entries = nullptr;  // [n * W] sorted (point | sign << 31)
+  void* buckets = nullptr;      // [nb] XYZZ
+  void* part_pt = nullptr;      // [2 * T] XYZZ partial sums of buckets split across threads
+  uint32_t* part_gb = nullptr;  // [2 * T]
+  void* chunk = nullptr;        // bucket-reduction partials
+  void* result = nullptr;       // 1 XYZZ
+  size_t cap_nb = 0, cap_entries = 0, cap_bucket_bytes = 0, cap_part_bytes = 0, cap_chunk_bytes = 0;
+  int part_threads = 0;
+};
+
+struct MsmPlan {
+  int c;        // window bits
+  int nwin;     // ceil(256 / c)
+  int copies;   // precomputed multiples per base (1 = none)
+  int nsets;    // bucket sets = ceil(nwin / copies)
+  uint32_t nbuckets_per_set;  // 2^(c-1)
+};
+
+struct Bases {  // device-resident base table (a proving-key query or a standalone upload)
+  int group;        // 1 = G1, 2 = G2
+  uint64_t n;       // points per copy
+  MsmPlan plan;
+  void* pts;        // [copies][n] affine
+};
+
+}  // namespace ctg
+
+struct ctg_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  bool own_stream = true;
+  std::string last_error;
+  uint64_t launches = 0;
+  std::map<int, ctg::NttDomain> domains;
+  ctg::MsmWorkspace ws[2];
+  void* scratch = nullptr; size_t scratch_bytes = 0;     // general device scratch (staging)
+  void* pinned = nullptr; size_t pinned_bytes = 0;       // pinned host staging
+  cudaEvent_t ev[16];
+  bool events_ready = false;
+};
+
+struct ctg_bases { ctg::Bases b; };
+
+namespace ctg {
+
+#define CTG_CUDA(ctx, call)                                                                  \
+  do {                                                                                       \
+    cudaError_t e__ = (call);                                                                \
+    if (e__ != cudaSuccess) {                                                                \
+      (ctx)->last_error = std::string(#call) + ": " + cudaGetErrorString(e__);               \
+      return CTG_ERR_CUDA;                                                                   \
+    }                                                                                        \
+  } while (0)
+#define CTG_TRY(expr)            \
+  do {                           \
+    int32_t rc__ = (expr);       \
+    if (rc__ != CTG_OK) return rc__; \
+  } while (0)
+#define CTG_KERNEL_CHECK(ctx)                                                                \
+  do {                                                                                       \
+    (ctx)->launches++;                                                                       \
+    cudaError_t e__ = cudaGetLastError();                                                    \
+    if (e__ != cudaSuccess) {                                                                \
+      (ctx)->last_error = std::string("kernel launch: ") + cudaGetErrorString(e__);          \
+      return CTG_ERR_CUDA;                                                                   \
+    }                                                                                        \
+  } while (0)
+
+int32_t fail(ctg_ctx* ctx, int32_t code, const std::string& msg);
+int32_t ensure_scratch(ctg_ctx* ctx, size_t bytes);
+int32_t ensure_pinned(ctg_ctx* ctx, size_t bytes);
+
+// ntt.cu
+int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out);
+// natural order in, natural order out (ark-poly Radix2EvaluationDomain::{fft,ifft,coset_fft,coset_ifft}_in_place)
+int32_t ntt_run(ctg_ctx* ctx, Fr* d_data, int log_n, int inverse, int coset, cudaStream_t st);
+// witness-map building blocks: no bit-reversal passes (see ntt.cu)
+int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);      // natural in, natural out
+int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);        // natural in, bit-reversed out
+
+// msm_g1.cu / msm_g2.cu
+MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override);
+int32_t msm_g1_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,
+                   G1XYZZ* d_out, cudaStream_t st, float* stage_ms);
+int32_t msm_g2_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,
+                   G2XYZZ* d_out, cudaStream_t st, float* stage_ms);
+int32_t g1_precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st);
+int32_t g2_precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st);
+int32_t g1_to_affine_dev(ctg_ctx* ctx, const G1XYZZ* d_in, G1Affine* d_out, int count, cudaStream_t st);
+int32_t g2_to_affine_dev(ctg_ctx* ctx, const G2XYZZ* d_in, G2Affine* d_out, int count, cudaStream_t st);
+int32_t g1_progression_dev(ctg_ctx* ctx, const G1Affine& g, const Fr& a, const Fr& b, uint64_t n, G1Affine* d_out, cudaStream_t st);
+int32_t g2_progression_dev(ctg_ctx* ctx, const G2Affine& g, const Fr& a, const Fr& b, uint64_t n, G2Affine* d_out, cudaStream_t st);
+int32_t g1_combine_dev(ctg_ctx* ctx, const G1XYZZ* d_in, uint32_t k, G1Affine* d_out_affine, G1XYZZ* d_out_xyzz, cudaStream_t st);
+int32_t g2_combine_dev(ctg_ctx* ctx, const G2XYZZ* d_in, uint32_t k, G2Affine* d_out_affine, G2XYZZ* d_out_xyzz, cudaStream_t st);
+void msm_ws_free(MsmWorkspace& ws);
+
+}  // namespace ctg

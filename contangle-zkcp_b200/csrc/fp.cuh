@@ -1,0 +1,242 @@
+// Montgomery prime-field arithmetic on 32-bit limbs for BLS12-381 Fr (8 limbs, R = 2^256)
+// and Fq (12 limbs, R = 2^384) -- the same R arkworks uses with 64-bit limbs, so a host
+// Fp256/Fp384 memory image is bit-identical to the device limb array.
+// Replaces: ark-ff 0.3.0 fields/models/{fp_256,fp_384}.rs (mul_assign / add_assign /
+// sub_assign / into_repr), reached from the reference at lib/src/zk/encryption.rs:76.
+//
+// mont_mul keeps the running sum T as two interleaved carry chains:
+//   E holds limbs 0..N-1, O holds limbs 1..N, T = E + 2^32 * O.
+// A row adds a*b_i: the products a_j*b_i with even j tile E without overlap, those with
+// odd j tile O, so each is one clean lo/hi carry chain (IMAD.WIDE.X after ptxas pairing).
+// The Montgomery step adds m*p the same way, leaving E[0] = 0; dividing by 2^32 then
+// swaps the roles (O becomes the limb-0 chain) and the old E, now two limbs out of phase,
+// is re-aligned for free inside the next row's multiply-add (register renaming once
+// unrolled).  All values stay < 2^(32(N+1)) because T < 2p before each row, so neither
+// chain can carry out of its top limb.
+#pragma once
+#include "ptx.cuh"
+
+namespace ctg {
+
+template <int N> struct Limbs { uint32_t v[N]; };
+
+struct FrParams {
+  static constexpr int N = 8;
+  static constexpr uint32_t INV = 0xffffffffu;  // -r^-1 mod 2^32
+  CTG_HD static constexpr uint32_t mod(int i) {
+    constexpr uint32_t m[8] = {0x00000001u, 0xffffffffu, 0xfffe5bfeu, 0x53bda402u, 0x09a1d805u, 0x3339d808u, 0x299d7d48u, 0x73eda753u};
+    return m[i];
+  }
+  CTG_HD static constexpr uint32_t one(int i) {  // R mod r
+    constexpr uint32_t m[8] = {0xfffffffeu, 0x00000001u, 0x00034802u, 0x5884b7fau, 0xecbc4ff5u, 0x998c4fefu, 0xacc5056fu, 0x1824b159u};
+    return m[i];
+  }
+  CTG_HD static constexpr uint32_t r2(int i) {  // R^2 mod r
+    constexpr uint32_t m[8] = {0xf3f29c6du, 0xc999e990u, 0x87925c23u, 0x2b6cedcbu, 0x7254398fu, 0x05d31496u, 0x9f59ff11u, 0x0748d9d9u};
+    return m[i];
+  }
+};
+
+struct FqParams {
+  static constexpr int N = 12;
+  static constexpr uint32_t INV = 0xfffcfffdu;  // -p^-1 mod 2^32
+  CTG_HD static constexpr uint32_t mod(int i) {
+    constexpr uint32_t m[12] = {0xffffaaabu, 0xb9feffffu, 0xb153ffffu, 0x1eabfffeu, 0xf6b0f624u, 0x6730d2a0u,
+                                0xf38512bfu, 0x64774b84u, 0x434bacd7u, 0x4b1ba7b6u, 0x397fe69au, 0x1a0111eau};
+    return m[i];
+  }
+  CTG_HD static constexpr uint32_t one(int i) {  // R mod p
+    constexpr uint32_t m[12] = {0x0002fffdu, 0x76090000u, 0xc40c0002u, 0xebf4000bu, 0x53c758bau, 0x5f489857u,
+                                0x70525745u, 0x77ce5853u, 0xa256ec6du, 0x5c071a97u, 0xfa80e493u, 0x15f65ec3u};
+    return m[i];
+  }
+  CTG_HD static constexpr uint32_t r2(int i) {  // R^2 mod p
+    constexpr uint32_t m[12] = {0x1c341746u, 0xf4df1f34u, 0x09d104f1u, 0x0a76e6a6u, 0x4c95b6d5u, 0x8de5476cu,
+                                0x939d83c0u, 0x67eb88a9u, 0xb519952du, 0x9a793e85u, 0x92cae3aau, 0x11988fe5u};
+    return m[i];
+  }
+};
+
+template <class P> struct alignas(16) Fp {
+  static constexpr int N = P::N;
+  uint32_t v[N];
+
+  CTG_HD static Fp zero() { Fp r;
+#pragma unroll
+    for (int i = 0; i < N; i++) r.v[i] = 0;
+    return r; }
+  CTG_HD static Fp one() { Fp r;
+#pragma unroll
+    for (int i = 0; i < N; i++) r.v[i] = P::one(i);
+    return r; }
+  CTG_HD bool is_zero() const { uint32_t o = 0;
+#pragma unroll
+    for (int i = 0; i < N; i++) o |= v[i];
+    return o == 0; }
+  CTG_HD bool eq(const Fp& b) const { uint32_t o = 0;
+#pragma unroll
+    for (int i = 0; i < N; i++) o |= v[i] ^ b.v[i];
+    return o == 0; }
+
+  // r = a - p if a >= p else a   (a < 2p)
+  CTG_HD static void reduce_once(uint32_t* a) {
+    uint32_t t[N];
+    t[0] = ptx::sub_cc(a[0], P::mod(0));
+#pragma unroll
+    for (int i = 1; i < N; i++) t[i] = ptx::subc_cc(a[i], P::mod(i));
+    uint32_t borrow = ptx::subc(0, 0);  // 0xffffffff when a < p
+#pragma unroll
+    for (int i = 0; i < N; i++) a[i] = borrow ? a[i] : t[i];
+  }
+
+  CTG_HD friend Fp operator+(const Fp& a, const Fp& b) {
+    Fp r;
+    r.v[0] = ptx::add_cc(a.v[0], b.v[0]);
+#pragma unroll
+    for (int i = 1; i < N - 1; i++) r.v[i] = ptx::addc_cc(a.v[i], b.v[i]);
+    r.v[N - 1] = ptx::addc(a.v[N - 1], b.v[N - 1]);  // 2p < 2^(32N): no carry out
+    reduce_once(r.v);
+    return r;
+  }
+  CTG_HD friend Fp operator-(const Fp& a, const Fp& b) {
+    Fp r;
+    r.v[0] = ptx::sub_cc(a.v[0], b.v[0]);
+#pragma unroll
+    for (int i = 1; i < N; i++) r.v[i] = ptx::subc_cc(a.v[i], b.v[i]);
+    uint32_t mask = ptx::subc(0, 0);  // all ones on borrow
+    r.v[0] = ptx::add_cc(r.v[0], P::mod(0) & mask);
+#pragma unroll
+    for (int i = 1; i < N - 1; i++) r.v[i] = ptx::addc_cc(r.v[i], P::mod(i) & mask);
+    r.v[N - 1] = ptx::addc(r.v[N - 1], P::mod(N - 1) & mask);
+    return r;
+  }
+  CTG_HD Fp neg() const { return zero() - *this; }
+  CTG_HD Fp dbl() const { return *this + *this; }
+
+  // --- Montgomery product ------------------------------------------------------------
+  // add m*p into (E at limbs 0.., O at limbs 1..); leaves E[0] == 0
+  CTG_HD static void redc_row(uint32_t* E, uint32_t* O) {
+    const uint32_t m = ptx::mul_lo(E[0], P::INV);
+    O[0] = ptx::mad_lo_cc(P::mod(1), m, O[0]);
+    O[1] = ptx::madc_hi_cc(P::mod(1), m, O[1]);
+#pragma unroll
+    for (int j = 3; j < N; j += 2) {
+      O[j - 1] = ptx::madc_lo_cc(P::mod(j), m, O[j - 1]);
+      if (j == N - 1) O[j] = ptx::madc_hi(P::mod(j), m, O[j]);
+      else O[j] = ptx::madc_hi_cc(P::mod(j), m, O[j]);
+    }
+    E[0] = ptx::mad_lo_cc(P::mod(0), m, E[0]);
+    E[1] = ptx::madc_hi_cc(P::mod(0), m, E[1]);
+#pragma unroll
+    for (int j = 2; j < N; j += 2) {
+      E[j] = ptx::madc_lo_cc(P::mod(j), m, E[j]);
+      E[j + 1] = ptx::madc_hi_cc(P::mod(j), m, E[j + 1]);
+    }
+    O[N - 1] = ptx::addc(O[N - 1], 0);
+  }
+  // E: limbs 0..N-1 (aligned); Oold: previous limb-0 chain, entry k sits at limb k-1.
+  CTG_HD static void mad_row(uint32_t* E, uint32_t* O, const uint32_t* a, uint32_t bi) {
+    E[0] = ptx::add_cc(E[0], O[1]);  // orphan limb; its carry enters limb 1 = head of the O chain
+#pragma unroll
+    for (int j = 1; j < N - 1; j += 2) {
+      O[j - 1] = ptx::madc_lo_cc(a[j], bi, O[j + 1]);
+      O[j] = ptx::madc_hi_cc(a[j], bi, O[j + 2]);
+    }
+    O[N - 2] = ptx::madc_lo_cc(a[N - 1], bi, 0);
+    O[N - 1] = ptx::madc_hi(a[N - 1], bi, 0);
+    E[0] = ptx::mad_lo_cc(a[0], bi, E[0]);
+    E[1] = ptx::madc_hi_cc(a[0], bi, E[1]);
+#pragma unroll
+    for (int j = 2; j < N; j += 2) {
+      E[j] = ptx::madc_lo_cc(a[j], bi, E[j]);
+      E[j + 1] = ptx::madc_hi_cc(a[j], bi, E[j + 1]);
+    }
+    O[N - 1] = ptx::addc(O[N - 1], 0);
+  }
+
+  CTG_HD friend Fp operator*(const Fp& a, const Fp& b) {
+    uint32_t ev[N], od[N];
+#pragma unroll
+    for (int j = 0; j < N; j += 2) {
+      ev[j] = ptx::mul_lo(a.v[j], b.v[0]);
+      ev[j + 1] = ptx::mul_hi(a.v[j], b.v[0]);
+      od[j] = ptx::mul_lo(a.v[j + 1], b.v[0]);
+      od[j + 1] = ptx::mul_hi(a.v[j + 1], b.v[0]);
+    }
+    redc_row(ev, od);
+#pragma unroll
+    for (int i = 1; i < N; i += 2) {
+      mad_row(od, ev, a.v, b.v[i]);
+      redc_row(od, ev);
+      if (i + 1 < N) {
+        mad_row(ev, od, a.v, b.v[i + 1]);
+        redc_row(ev, od);
+      }
+    }
+    // N even: the last row ran with E = od, O = ev.  Result limb k = ev[k] + od[k+1].
+    Fp r;
+    r.v[0] = ptx::add_cc(ev[0], od[1]);
+#pragma unroll
+    for (int k = 1; k < N - 1; k++) r.v[k] = ptx::addc_cc(ev[k], od[k + 1]);
+    r.v[N - 1] = ptx::addc(ev[N - 1], 0);
+    reduce_once(r.v);
+    return r;
+  }
+  CTG_HD Fp sqr() const { return *this * *this; }
+
+  CTG_HD Fp from_mont() const {  // canonical integer image (ark-ff into_repr)
+    Fp o = zero();
+    o.v[0] = 1;
+    return *this * o;
+  }
+  CTG_HD Fp to_mont() const {
+    Fp r2;
+#pragma unroll
+    for (int i = 0; i < N; i++) r2.v[i] = P::r2(i);
+    return *this * r2;
+  }
+  // a^(p-2); cold path (final to-affine only)
+  CTG_HD_COLD Fp inv() const {
+    uint32_t e[N];
+    e[0] = ptx::sub_cc(P::mod(0), 2);
+#pragma unroll
+    for (int i = 1; i < N; i++) e[i] = ptx::subc_cc(P::mod(i), 0);
+    Fp acc = one();
+    for (int i = N * 32 - 1; i >= 0; i--) {
+      acc = acc.sqr();
+      if ((e[i >> 5] >> (i & 31)) & 1) acc = acc * *this;
+    }
+    return acc;
+  }
+};
+
+typedef Fp<FrParams> Fr;
+typedef Fp<FqParams> Fq;
+
+// Fq2 = Fq[u]/(u^2 + 1)   (ark-ff fp2.rs with ark-bls12-381 NONRESIDUE = -1)
+struct Fq2 {
+  Fq c0, c1;
+  CTG_HD static Fq2 zero() { return {Fq::zero(), Fq::zero()}; }
+  CTG_HD static Fq2 one() { return {Fq::one(), Fq::zero()}; }
+  CTG_HD bool is_zero() const { return c0.is_zero() && c1.is_zero(); }
+  CTG_HD bool eq(const Fq2& b) const { return c0.eq(b.c0) && c1.eq(b.c1); }
+  CTG_HD friend Fq2 operator+(const Fq2& a, const Fq2& b) { return {a.c0 + b.c0, a.c1 + b.c1}; }
+  CTG_HD friend Fq2 operator-(const Fq2& a, const Fq2& b) { return {a.c0 - b.c0, a.c1 - b.c1}; }
+  CTG_HD Fq2 neg() const { return {c0.neg(), c1.neg()}; }
+  CTG_HD Fq2 dbl() const { return {c0.dbl(), c1.dbl()}; }
+  CTG_HD friend Fq2 operator*(const Fq2& a, const Fq2& b) {
+    Fq v0 = a.c0 * b.c0, v1 = a.c1 * b.c1;
+    Fq s = (a.c0 + a.c1) * (b.c0 + b.c1);
+    return {v0 - v1, s - v0 - v1};
+  }
+  CTG_HD Fq2 sqr() const {
+    Fq t = c0 * c1;
+    return {(c0 + c1) * (c0 - c1), t + t};
+  }
+  CTG_HD Fq2 inv() const {
+    Fq n = (c0.sqr() + c1.sqr()).inv();
+    return {c0 * n, (c1 * n).neg()};
+  }
+};
+
+}  // namespace ctg

@@ -1,0 +1,512 @@
+// Pippenger multi-scalar multiplication with signed-digit windows, templated on the base
+// field (Fq -> G1, Fq2 -> G2).  Replaces ark-ec 0.3.0 VariableBaseMSM::multi_scalar_mul
+// (msm/variable_base.rs), called five times per proof by ark-groth16's create_proof, which
+// the reference reaches from Groth16::prove at lib/src/zk/encryption.rs:76.
+//
+// Pipeline (all on one stream):
+//   1. msm_count     scalar -> signed digits, histogram of (bucket set, |digit|-1)    [warp-aggregated atomics]
+//   2. msm_scan      exclusive prefix sum -> bucket start offsets
+//   3. msm_scatter   counting sort: entries[] = point index | sign << 31, grouped by bucket
+//   4. msm_accumulate  the sorted entry list is cut into equal slices, one per thread; each thread
+//                    walks its slice adding affine bases into an XYZZ accumulator (8M + 2S) and
+//                    emits a bucket sum whenever the bucket id changes.  Work per thread is
+//                    identical whatever the scalar distribution (zeros, ones, bytes, uniform).
+//   5. msm_fixup     buckets cut by a slice boundary: their partial sums are added by one warp each
+//   6. msm_bucket_reduce  sum_b (b+1) * bucket[b] with chunked running sums, all chunks in parallel
+//   7. msm_set_sum / msm_horner  per-set totals, then sum_g 2^(c g) S_g
+// Windows w = j * G + g use the precomputed multiple 2^(c G j) * P (copy j of the base table),
+// so only G = ceil(W / copies) bucket sets exist; with copies = W there is a single set and no
+// doubling chain at the end.
+#pragma once
+#include "ctg_internal.h"
+#include "msm_digits.cuh"
+
+namespace ctg {
+
+static constexpr uint32_t kNoBucket = 0xffffffffu;
+static constexpr uint32_t kHeadBit = 0x80000000u;
+
+template <class F> __device__ __forceinline__ void ld_affine(Affine<F>& p, const Affine<F>* src) {
+  constexpr int NW = sizeof(Affine<F>) / 16;
+  const uint4* q = reinterpret_cast<const uint4*>(src);
+  uint4* d = reinterpret_cast<uint4*>(&p);
+#pragma unroll
+  for (int i = 0; i < NW; i++) d[i] = __ldg(q + i);
+}
+template <class T> __device__ __forceinline__ void copy16(T& dst, const T& src) {
+  constexpr int NW = sizeof(T) / 16;
+  const uint4* q = reinterpret_cast<const uint4*>(&src);
+  uint4* d = reinterpret_cast<uint4*>(&dst);
+#pragma unroll
+  for (int i = 0; i < NW; i++) d[i] = q[i];
+}
+
+__device__ __forceinline__ Fr load_scalar(const uint32_t* scalars, uint64_t i, int mont) {
+  const uint4* q = reinterpret_cast<const uint4*>(scalars + 8 * i);
+  uint4 a = __ldg(q), b = __ldg(q + 1);
+  Fr s;
+  s.v[0] = a.x; s.v[1] = a.y; s.v[2] = a.z; s.v[3] = a.w;
+  s.v[4] = b.x; s.v[5] = b.y; s.v[6] = b.z; s.v[7] = b.w;
+  return mont ? s.from_mont() : s;
+}
+
+// ---- 1. histogram -------------------------------------------------------------------------
+template <class F> __global__ void msm_count_kernel(const uint32_t* __restrict__ scalars, uint64_t n, int mont, MsmPlan plan, uint32_t* counts) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t n32 = (n + 31) & ~31ull;
+  const unsigned lane = threadIdx.x & 31;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += stride) {
+    const bool valid = i < n;
+    uint32_t k[8];
+    if (valid) { Fr s = load_scalar(scalars, i, mont);
+#pragma unroll
+      for (int j = 0; j < 8; j++) k[j] = s.v[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; j++) k[j] = 0;
+    }
+    uint32_t carry = 0;
+    for (int w = 0; w < plan.nwin; w++) {
+      int32_t d = msm_signed_digit(k, plan.c, w, plan.nwin, carry);
+      uint32_t key = kNoBucket;
+      if (d != 0) key = (uint32_t)(w % plan.nsets) * plan.nbuckets_per_set + (uint32_t)((d < 0 ? -d : d) - 1);
+      unsigned peers = __match_any_sync(0xffffffffu, key);
+      if (key != kNoBucket && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&counts[key], (uint32_t)__popc(peers));
+    }
+  }
+}
+
+// ---- 2. exclusive scan (one CTA; nb <= 2^20) ------------------------------------------------
+template <class F> __global__ void __launch_bounds__(1024) msm_scan_kernel(uint32_t* counts, uint32_t* cursor, uint32_t nb) {
+  __shared__ uint32_t sums[1024];
+  const uint32_t tid = threadIdx.x;
+  const uint32_t per = (nb + 1023) / 1024;
+  const uint32_t lo = min(nb, tid * per), hi = min(nb, lo + per);
+  uint32_t s = 0;
+  for (uint32_t i = lo; i < hi; i++) s += counts[i];
+  sums[tid] = s;
+  __syncthreads();
+  for (uint32_t off = 1; off < 1024; off <<= 1) {
+    uint32_t v = tid >= off ? sums[tid - off] : 0;
+    __syncthreads();
+    sums[tid] += v;
+    __syncthreads();
+  }
+  uint32_t run = sums[tid] - s;
+  for (uint32_t i = lo; i < hi; i++) {
+    uint32_t c = counts[i];
+    counts[i] = run;
+    cursor[i] = run;
+    run += c;
+  }
+  if (tid == 1023) counts[nb] = sums[1023];
+}
+
+// ---- 3. scatter ---------------------------------------------------------------------------
+template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, uint64_t n, int mont, MsmPlan plan, uint32_t* cursor,
+                                                      uint32_t* entries) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t n32 = (n + 31) & ~31ull;
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += stride) {
+    const bool valid = i < n;
+    uint32_t k[8];
+    if (valid) { Fr s = load_scalar(scalars, i, mont);
+#pragma unroll
+      for (int j = 0; j < 8; j++) k[j] = s.v[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; j++) k[j] = 0;
+    }
+    uint32_t carry = 0;
+    for (int w = 0; w < plan.nwin; w++) {
+      int32_t d = msm_signed_digit(k, plan.c, w, plan.nwin, carry);
+      uint32_t key = kNoBucket;
+      if (d != 0) key = (uint32_t)(w % plan.nsets) * plan.nbuckets_per_set + (uint32_t)((d < 0 ? -d : d) - 1);
+      unsigned peers = __match_any_sync(0xffffffffu, key);
+      int leader = __ffs(peers) - 1;
+      uint32_t base = 0;
+      if (key != kNoBucket && (int)lane == leader) base = atomicAdd(&cursor[key], (uint32_t)__popc(peers));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (key != kNoBucket) {
+        uint32_t copy = (uint32_t)(w / plan.nsets);
+        entries[base + __popc(peers & lt_mask)] = (uint32_t)(copy * n + i) | (d < 0 ? 0x80000000u : 0u);
+      }
+    }
+  }
+}
+
+// ---- 4. bucket accumulation (dominant kernel): msm_acc.cuh, compiled in its own translation unit
+template <class F> int accumulate_max_blocks_per_sm();
+template <class F>
+void accumulate_launch(int blocks, cudaStream_t st, const Affine<F>* bases, const uint32_t* entries, const uint32_t* starts, uint32_t nb,
+                       XYZZ<F>* buckets, XYZZ<F>* part_pt, uint32_t* part_gb);
+
+// ---- 5. buckets cut by slice boundaries -------------------------------------------------------
+template <class F> __device__ __forceinline__ XYZZ<F> warp_sum(XYZZ<F> acc, XYZZ<F>* sh /* 32 per warp */, unsigned lane) {
+  copy16(sh[lane], acc);
+  __syncwarp();
+  for (int off = 16; off >= 1; off >>= 1) {
+    if ((int)lane < off) {
+      XYZZ<F> o;
+      copy16(o, sh[lane + off]);
+      acc = xyzz_add(acc, o);
+      copy16(sh[lane], acc);
+    }
+    __syncwarp();
+  }
+  return acc;
+}
+
+template <class F> __global__ void __launch_bounds__(64) msm_fixup_kernel(const XYZZ<F>* part_pt, const uint32_t* __restrict__ part_gb, uint32_t nslots,
+                                                                         XYZZ<F>* buckets) {
+  __shared__ XYZZ<F> sh[2][32];
+  const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const uint32_t slot0 = (blockIdx.x * 2 + wib) * 32;
+  if (slot0 >= nslots) return;
+  const uint32_t my = slot0 + lane;
+  const uint32_t tag = my < nslots ? part_gb[my] : kNoBucket;
+  unsigned heads = __ballot_sync(0xffffffffu, tag != kNoBucket && (tag & kHeadBit));
+  while (heads) {
+    const int h = __ffs(heads) - 1;
+    heads &= heads - 1;
+    const uint32_t gb = __shfl_sync(0xffffffffu, tag, h) & ~kHeadBit;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (uint32_t base = slot0 + h;; base += 32) {
+      const uint32_t s = base + lane;
+      const uint32_t g = s < nslots ? part_gb[s] : kNoBucket;
+      const bool mine = g != kNoBucket && (g & ~kHeadBit) == gb;
+      if (mine) {
+        XYZZ<F> o;
+        copy16(o, part_pt[s]);
+        acc = xyzz_add(acc, o);
+      }
+      const bool stop = s >= nslots || (g != kNoBucket && (g & ~kHeadBit) != gb);
+      if (__any_sync(0xffffffffu, stop)) break;
+    }
+    acc = warp_sum(acc, sh[wib], lane);
+    if (lane == 0) copy16(buckets[gb], acc);
+    __syncwarp();
+  }
+}
+
+// ---- 6. bucket reduction ----------------------------------------------------------------------
+// grid = (blocks per set, nsets); each thread owns L consecutive buckets.
+template <class F, int TB> __global__ void __launch_bounds__(TB) msm_bucket_reduce_kernel(const XYZZ<F>* __restrict__ buckets, uint32_t B, int L,
+                                                                                         XYZZ<F>* chunk_out) {
+  __shared__ XYZZ<F> sh[TB];
+  const uint32_t set = blockIdx.y;
+  const uint32_t ch = blockIdx.x * TB + threadIdx.x;
+  const uint64_t off = (uint64_t)ch * L;
+  XYZZ<F> run = XYZZ<F>::inf(), wt = XYZZ<F>::inf();
+  if (off < B) {
+    for (int i = L - 1; i >= 0; i--) {
+      const uint64_t bidx = off + i;
+      if (bidx < B) {
+        XYZZ<F> o;
+        copy16(o, buckets[(uint64_t)set * B + bidx]);
+        run = xyzz_add(run, o);
+      }
+      wt = xyzz_add(wt, run);
+    }
+    // wt = sum (b - off + 1) * bucket[b];  add off * run
+    if (off != 0 && !run.is_inf()) {
+      XYZZ<F> m = XYZZ<F>::inf();
+      uint32_t o32 = (uint32_t)off;
+      for (int bit = 31 - __clz(o32); bit >= 0; bit--) {
+        m = xyzz_dbl(m);
+        if ((o32 >> bit) & 1) m = xyzz_add(m, run);
+      }
+      wt = xyzz_add(wt, m);
+    }
+  }
+  copy16(sh[threadIdx.x], wt);
+  __syncthreads();
+  for (int s = TB / 2; s >= 1; s >>= 1) {
+    if ((int)threadIdx.x < s) {
+      XYZZ<F> o;
+      copy16(o, sh[threadIdx.x + s]);
+      wt = xyzz_add(wt, o);
+      copy16(sh[threadIdx.x], wt);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) copy16(chunk_out[(uint64_t)set * gridDim.x + blockIdx.x], wt);
+}
+
+// ---- 7. per-set totals and window combine -----------------------------------------------------
+// one CTA per set: sums `per_set` chunk results
+template <class F, int TB> __global__ void __launch_bounds__(TB) msm_set_sum_kernel(const XYZZ<F>* chunk, uint32_t per_set, XYZZ<F>* set_out) {
+  __shared__ XYZZ<F> sh[TB];
+  XYZZ<F> acc = XYZZ<F>::inf();
+  for (uint32_t i = threadIdx.x; i < per_set; i += TB) {
+    XYZZ<F> o;
+    copy16(o, chunk[(uint64_t)blockIdx.x * per_set + i]);
+    acc = xyzz_add(acc, o);
+  }
+  copy16(sh[threadIdx.x], acc);
+  __syncthreads();
+  for (int s = TB / 2; s >= 1; s >>= 1) {
+    if ((int)threadIdx.x < s) {
+      XYZZ<F> o;
+      copy16(o, sh[threadIdx.x + s]);
+      acc = xyzz_add(acc, o);
+      copy16(sh[threadIdx.x], acc);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) copy16(set_out[blockIdx.x], acc);
+}
+
+// sum_g 2^(c g) S_g, single thread (G - 1) * c doublings; G = 1 when every window is precomputed
+template <class F> __global__ void msm_horner_kernel(const XYZZ<F>* sets, int nsets, int c, XYZZ<F>* out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  XYZZ<F> acc;
+  copy16(acc, sets[nsets - 1]);
+  for (int g = nsets - 2; g >= 0; g--) {
+    for (int k = 0; k < c; k++) acc = xyzz_dbl(acc);
+    XYZZ<F> o;
+    copy16(o, sets[g]);
+    acc = xyzz_add(acc, o);
+  }
+  copy16(*out, acc);
+}
+
+// ---- small utilities ----------------------------------------------------------------------------
+template <class F> __global__ void to_affine_kernel(const XYZZ<F>* in, Affine<F>* out, int count) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  XYZZ<F> p;
+  copy16(p, in[i]);
+  Affine<F> a = xyzz_to_affine(p);
+  copy16(out[i], a);
+}
+
+// out = affine(sum_i in[i]); one warp
+template <class F> __global__ void __launch_bounds__(32) combine_kernel(const XYZZ<F>* in, uint32_t k, Affine<F>* out_affine, XYZZ<F>* out_xyzz) {
+  __shared__ XYZZ<F> sh[32];
+  const unsigned lane = threadIdx.x;
+  XYZZ<F> acc = XYZZ<F>::inf();
+  for (uint32_t i = lane; i < k; i += 32) {
+    XYZZ<F> o;
+    copy16(o, in[i]);
+    acc = xyzz_add(acc, o);
+  }
+  acc = warp_sum(acc, sh, lane);
+  if (lane == 0) {
+    if (out_xyzz) copy16(*out_xyzz, acc);
+    if (out_affine) {
+      Affine<F> a = xyzz_to_affine(acc);
+      copy16(*out_affine, a);
+    }
+  }
+}
+
+// P_i = (a + i*b) * g for i in [0, n): each thread owns CH consecutive points
+template <class F, int CH> __global__ void __launch_bounds__(128) progression_kernel(Affine<F> g, Affine<F> step, Fr a, Fr b, uint64_t n, Affine<F>* out) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t i0 = t * CH;
+  if (i0 >= n) return;
+  Fr idx = Fr::zero();
+  idx.v[0] = (uint32_t)i0;
+  idx.v[1] = (uint32_t)(i0 >> 32);
+  Fr k = (a + b * idx.to_mont()).from_mont();
+  XYZZ<F> pts[CH];
+  XYZZ<F> acc = xyzz_mul(XYZZ<F>::from_affine(g), k.v);
+  F prod[CH];
+  F run = F::one();
+#pragma unroll 1
+  for (int j = 0; j < CH; j++) {
+    pts[j] = acc;
+    prod[j] = run;                        // product of the denominators before j
+    if (!acc.is_inf()) run = run * (acc.ZZ * acc.ZZZ);
+    acc = xyzz_madd(acc, step);
+  }
+  F inv = run.inv();
+#pragma unroll 1
+  for (int j = CH - 1; j >= 0; j--) {
+    if (i0 + j >= n) { if (!pts[j].is_inf()) inv = inv * (pts[j].ZZ * pts[j].ZZZ); continue; }
+    Affine<F> o = Affine<F>::inf();
+    if (!pts[j].is_inf()) {
+      F t = inv * prod[j];                // 1 / (ZZ * ZZZ)
+      inv = inv * (pts[j].ZZ * pts[j].ZZZ);
+      o.x = pts[j].X * (t * pts[j].ZZZ);
+      o.y = pts[j].Y * (t * pts[j].ZZ);
+    }
+    copy16(out[i0 + j], o);
+  }
+}
+
+// copy j+1 = 2^(shift) * copy j, for j < copies-1; thread per base point; batch inversion per thread
+template <class F, int MAXC> __global__ void __launch_bounds__(128) precompute_kernel(Affine<F>* pts, uint64_t n, int copies, int shift) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Affine<F> p0;
+  copy16(p0, pts[i]);
+  XYZZ<F> cur = XYZZ<F>::from_affine(p0);
+  XYZZ<F> tab[MAXC];
+  F prod[MAXC];
+  F run = F::one();
+#pragma unroll 1
+  for (int j = 1; j < copies; j++) {
+    for (int k = 0; k < shift; k++) cur = xyzz_dbl(cur);
+    tab[j] = cur;
+    prod[j] = run;
+    if (!cur.is_inf()) run = run * (cur.ZZ * cur.ZZZ);
+  }
+  F inv = run.inv();
+#pragma unroll 1
+  for (int j = copies - 1; j >= 1; j--) {
+    Affine<F> o = Affine<F>::inf();
+    if (!tab[j].is_inf()) {
+      F t = inv * prod[j];
+      inv = inv * (tab[j].ZZ * tab[j].ZZZ);
+      o.x = tab[j].X * (t * tab[j].ZZZ);
+      o.y = tab[j].Y * (t * tab[j].ZZ);
+    }
+    copy16(pts[(uint64_t)j * n + i], o);
+  }
+}
+
+// ---- host orchestration -------------------------------------------------------------------------
+template <class F> struct MsmHost {
+  static constexpr int kReduceTB = 64;
+  static constexpr int kReduceL = 8;
+
+  static int32_t ensure_ws(ctg_ctx* ctx, MsmWorkspace& ws, const MsmPlan& plan, uint64_t n, int max_threads) {
+    const size_t nb = (size_t)plan.nsets * plan.nbuckets_per_set;
+    const size_t ne = (size_t)n * plan.nwin;
+    if (nb + 1 > ws.cap_nb) {
+      if (ws.counts) cudaFree(ws.counts);
+      if (ws.cursor) cudaFree(ws.cursor);
+      CTG_CUDA(ctx, cudaMalloc(&ws.counts, (nb + 1) * sizeof(uint32_t)));
+      CTG_CUDA(ctx, cudaMalloc(&ws.cursor, (nb + 1) * sizeof(uint32_t)));
+      ws.cap_nb = nb + 1;
+    }
+    if (ne > ws.cap_entries) {
+      if (ws.entries) cudaFree(ws.entries);
+      CTG_CUDA(ctx, cudaMalloc(&ws.entries, (ne ? ne : 1) * sizeof(uint32_t)));
+      ws.cap_entries = ne;
+    }
+    const size_t bb = nb * sizeof(XYZZ<F>);
+    if (bb > ws.cap_bucket_bytes) {
+      if (ws.buckets) cudaFree(ws.buckets);
+      CTG_CUDA(ctx, cudaMalloc(&ws.buckets, bb));
+      ws.cap_bucket_bytes = bb;
+    }
+    const size_t pb = (size_t)2 * max_threads * sizeof(XYZZ<F>);
+    if (pb > ws.cap_part_bytes) {
+      if (ws.part_pt) cudaFree(ws.part_pt);
+      if (ws.part_gb) cudaFree(ws.part_gb);
+      CTG_CUDA(ctx, cudaMalloc(&ws.part_pt, pb));
+      CTG_CUDA(ctx, cudaMalloc(&ws.part_gb, (size_t)2 * max_threads * sizeof(uint32_t)));
+      ws.cap_part_bytes = pb;
+    }
+    const size_t cb = (nb / kReduceL / kReduceTB + 2 * (size_t)plan.nsets + 64) * sizeof(XYZZ<F>);
+    if (cb > ws.cap_chunk_bytes) {
+      if (ws.chunk) cudaFree(ws.chunk);
+      CTG_CUDA(ctx, cudaMalloc(&ws.chunk, cb));
+      ws.cap_chunk_bytes = cb;
+    }
+    if (!ws.result) CTG_CUDA(ctx, cudaMalloc(&ws.result, sizeof(XYZZ<Fq2>)));
+    return CTG_OK;
+  }
+
+  static int32_t run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool mont, XYZZ<F>* d_out,
+                     cudaStream_t st, float* stage_ms) {
+    const MsmPlan& plan = bases.plan;
+    if (n > bases.n) return fail(ctx, CTG_ERR_INVALID, "msm: more scalars than bases");
+    if ((uint64_t)bases.n * plan.copies >= (1ull << 31)) return fail(ctx, CTG_ERR_INVALID, "msm: n * copies must be < 2^31");
+    if ((uint64_t)n * plan.nwin >= (1ull << 32)) return fail(ctx, CTG_ERR_INVALID, "msm: n * windows must be < 2^32");
+    if (n == 0) {
+      CTG_CUDA(ctx, cudaMemsetAsync(d_out, 0, sizeof(XYZZ<F>), st));
+      return CTG_OK;
+    }
+    // accumulate launch geometry
+    static int occ = 0;
+    if (!occ) {
+      occ = accumulate_max_blocks_per_sm<F>();
+      if (occ < 1) occ = 1;
+    }
+    const int max_blocks = ctx->sm_count * occ;
+    const int max_threads = max_blocks * 128;
+    CTG_TRY(ensure_ws(ctx, ws, plan, n, max_threads));
+    const uint32_t nb = (uint32_t)plan.nsets * plan.nbuckets_per_set;
+    XYZZ<F>* buckets = reinterpret_cast<XYZZ<F>*>(ws.buckets);
+    XYZZ<F>* part_pt = reinterpret_cast<XYZZ<F>*>(ws.part_pt);
+    XYZZ<F>* chunk = reinterpret_cast<XYZZ<F>*>(ws.chunk);
+    const bool timed = stage_ms != nullptr;
+    if (timed && !ctx->events_ready) {
+      for (auto& e : ctx->ev) CTG_CUDA(ctx, cudaEventCreate(&e));
+      ctx->events_ready = true;
+    }
+    if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+
+    CTG_CUDA(ctx, cudaMemsetAsync(ws.counts, 0, (size_t)(nb + 1) * sizeof(uint32_t), st));
+    const int dig_blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx->sm_count * 8);
+    msm_count_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, mont ? 1 : 0, plan, ws.counts);
+    CTG_KERNEL_CHECK(ctx);
+    msm_scan_kernel<F><<<1, 1024, 0, st>>>(ws.counts, ws.cursor, nb);
+    CTG_KERNEL_CHECK(ctx);
+    msm_scatter_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, mont ? 1 : 0, plan, ws.cursor, ws.entries);
+    CTG_KERNEL_CHECK(ctx);
+    if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+
+    CTG_CUDA(ctx, cudaMemsetAsync(ws.buckets, 0, (size_t)nb * sizeof(XYZZ<F>), st));
+    uint64_t want_threads = ((uint64_t)n * plan.nwin + 15) / 16;
+    int blocks = (int)std::min<uint64_t>((want_threads + 127) / 128, (uint64_t)max_blocks);
+    if (blocks < 1) blocks = 1;
+    const uint32_t nslots = (uint32_t)blocks * 128 * 2;
+    accumulate_launch<F>(blocks, st, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, ws.counts, nb, buckets, part_pt, ws.part_gb);
+    CTG_KERNEL_CHECK(ctx);
+    msm_fixup_kernel<F><<<(nslots / 32 + 1) / 2, 64, 0, st>>>(part_pt, ws.part_gb, nslots, buckets);
+    CTG_KERNEL_CHECK(ctx);
+    if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
+
+    const uint32_t B = plan.nbuckets_per_set;
+    const uint32_t chunks = (B + kReduceL - 1) / kReduceL;
+    const uint32_t bps = (chunks + kReduceTB - 1) / kReduceTB;
+    dim3 grid(bps, plan.nsets);
+    msm_bucket_reduce_kernel<F, kReduceTB><<<grid, kReduceTB, 0, st>>>(buckets, B, kReduceL, chunk);
+    CTG_KERNEL_CHECK(ctx);
+    XYZZ<F>* set_out = chunk + (size_t)bps * plan.nsets;
+    msm_set_sum_kernel<F, 64><<<plan.nsets, 64, 0, st>>>(chunk, bps, set_out);
+    CTG_KERNEL_CHECK(ctx);
+    msm_horner_kernel<F><<<1, 32, 0, st>>>(set_out, plan.nsets, plan.c, d_out);
+    CTG_KERNEL_CHECK(ctx);
+    if (timed) {
+      CTG_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
+      CTG_CUDA(ctx, cudaEventSynchronize(ctx->ev[3]));
+      for (int i = 0; i < 3; i++) CTG_CUDA(ctx, cudaEventElapsedTime(&stage_ms[i], ctx->ev[i], ctx->ev[i + 1]));
+    }
+    return CTG_OK;
+  }
+
+  static int32_t precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st) {
+    if (b.plan.copies <= 1) return CTG_OK;
+    if (b.plan.copies > 32) return fail(ctx, CTG_ERR_INVALID, "bases: at most 32 precomputed copies");
+    const int shift = b.plan.c * b.plan.nsets;
+    precompute_kernel<F, 32><<<(unsigned)((b.n + 127) / 128), 128, 0, st>>>(reinterpret_cast<Affine<F>*>(b.pts), b.n, b.plan.copies, shift);
+    CTG_KERNEL_CHECK(ctx);
+    return CTG_OK;
+  }
+
+  static int32_t to_affine(ctg_ctx* ctx, const XYZZ<F>* in, Affine<F>* out, int count, cudaStream_t st) {
+    to_affine_kernel<F><<<(count + 31) / 32, 32, 0, st>>>(in, out, count);
+    CTG_KERNEL_CHECK(ctx);
+    return CTG_OK;
+  }
+
+  static int32_t progression(ctg_ctx* ctx, const Affine<F>& g, const Fr& a, const Fr& b, uint64_t n, Affine<F>* d_out, cudaStream_t st) {
+    constexpr int CH = 16;
+    Fr bc = b.from_mont();
+    Affine<F> step = xyzz_to_affine(xyzz_mul(XYZZ<F>::from_affine(g), bc.v));  // host-side (emulated) one-off
+    const uint64_t threads = (n + CH - 1) / CH;
+    progression_kernel<F, CH><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(g, step, a, b, n, d_out);
+    CTG_KERNEL_CHECK(ctx);
+    return CTG_OK;
+  }
+};
+
+}  // namespace ctg

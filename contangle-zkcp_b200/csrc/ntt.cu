@@ -1,0 +1,346 @@
+// Radix-2 NTT over BLS12-381 Fr, shared-memory staged.
+// Replaces ark-poly 0.3.0 Radix2EvaluationDomain::{fft,ifft,coset_fft,coset_ifft}_in_place
+// (domain/radix2/fft.rs), reached from ark-groth16 R1CStoQAP::witness_map, i.e. from
+// Groth16::prove at /root/reference lib/src/zk/encryption.rs:76.
+//
+// A transform of 2^k points is split into passes of up to 8 (strided) or 11 (contiguous)
+// butterfly levels.  One CTA owns a tile of 2^11 elements (64 KB of shared memory, stored
+// as two 16-byte planes so that consecutive lanes hit consecutive banks), reads it from HBM
+// once with 128-bit loads in runs of >= 256 contiguous bytes, runs all levels of the pass in
+// shared memory, and writes it back once.  HBM traffic is therefore 64 B per element per
+// pass (+ the twiddle reads, which come from a per-domain table that mostly lives in L2).
+//
+// Two kernels' worth of dataflow are provided by one template:
+//   DIF (Gentleman-Sande): natural order in  -> bit-reversed out
+//   DIT (Cooley-Tukey):    bit-reversed in   -> natural order out
+// so the witness map (ifft -> coset_fft -> pointwise -> coset_ifft) never runs a separate
+// bit-reversal pass: ifft is DIF, the following coset_fft is DIT, the final coset_ifft is DIF
+// and its bit-reversed output is consumed by an MSM whose bases were permuted at key upload.
+// Coset shifts (g = 7), the 1/n of the inverse transform and their product are fused into the
+// first load / last store of a pass through per-domain power tables.
+#include <algorithm>
+
+#include "ctg_internal.h"
+
+namespace ctg {
+
+static constexpr int kTileLog = 11;     // elements per CTA tile
+static constexpr int kStridedLevels = 8;
+static constexpr int kThreads = 256;
+
+struct PowParams { Fr sq[32]; };  // base^(2^j)
+
+__global__ void pow_table_kernel(Fr* out, uint64_t n, PowParams p, Fr scale) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Fr acc = scale;
+  for (int j = 0; j < 32; j++)
+    if ((i >> j) & 1) acc = acc * p.sq[j];
+  out[i] = acc;
+}
+
+struct NttPass {
+  int log_n;
+  int log_blk;   // log2 of the sub-transform size at this pass
+  int S;         // butterfly levels in this pass
+  int log_tile;  // log2 elements per CTA
+  int dit;
+  const Fr* tw;        // w^k table of the full domain, k < n/2
+  const Fr* pre_tab;   // optional multiplier applied while loading (indexed by natural position)
+  const Fr* post_tab;  // optional multiplier applied while storing
+  int pre_bitrev, post_bitrev;  // data at that point is bit-reversed: table index = bitrev(address)
+  int post_const;      // multiply by post_c while storing
+  Fr post_c;
+};
+
+__device__ __forceinline__ Fr ld_fr(const uint4* lo, const uint4* hi, int i) {
+  Fr r;
+  uint4 a = lo[i], b = hi[i];
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ void st_fr(uint4* lo, uint4* hi, int i, const Fr& r) {
+  lo[i] = make_uint4(r.v[0], r.v[1], r.v[2], r.v[3]);
+  hi[i] = make_uint4(r.v[4], r.v[5], r.v[6], r.v[7]);
+}
+__device__ __forceinline__ Fr ldg_fr(const Fr* p) {
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  uint4 a = __ldg(q), b = __ldg(q + 1);
+  Fr r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ uint64_t bitrev_idx(uint64_t a, int log_n) {
+  return log_n == 0 ? 0 : (uint64_t)(__brev((uint32_t)a) >> (32 - log_n));
+}
+
+__global__ void __launch_bounds__(kThreads) ntt_pass_kernel(Fr* __restrict__ data, NttPass p) {
+  extern __shared__ uint4 smem[];
+  const int tile = 1 << p.log_tile;
+  uint4* lo = smem;
+  uint4* hi = smem + tile;
+  const int log_cpb = p.log_blk - p.S;    // columns per sub-transform
+  const int log_C = p.log_tile - p.S;     // columns per tile
+  const bool strided = log_cpb > log_C;
+  const int C = 1 << log_C;
+  const uint64_t tile_id = blockIdx.x;
+  uint64_t base;  // address of tile-local index 0
+  uint32_t j0 = 0;
+  if (strided) {
+    uint64_t q0 = tile_id << log_C;
+    uint64_t b = q0 >> log_cpb;
+    j0 = (uint32_t)(q0 & ((1ull << log_cpb) - 1));
+    base = (b << p.log_blk) + j0;
+  } else {
+    base = tile_id << p.log_tile;
+  }
+  auto addr_of = [&](int idx) -> uint64_t {
+    return strided ? base + ((uint64_t)(idx >> log_C) << log_cpb) + (idx & (C - 1)) : base + idx;
+  };
+
+  // ---- load tile (128-bit loads; runs of C*32 >= 256 contiguous bytes)
+  for (int e = threadIdx.x; e < tile; e += kThreads) {
+    uint64_t a = addr_of(e);
+    const uint4* g = reinterpret_cast<const uint4*>(data + a);
+    uint4 x = g[0], y = g[1];
+    if (p.pre_tab) {
+      Fr v;
+      v.v[0] = x.x; v.v[1] = x.y; v.v[2] = x.z; v.v[3] = x.w;
+      v.v[4] = y.x; v.v[5] = y.y; v.v[6] = y.z; v.v[7] = y.w;
+      uint64_t ti = p.pre_bitrev ? bitrev_idx(a, p.log_n) : a;
+      v = v * ldg_fr(p.pre_tab + ti);
+      st_fr(lo, hi, e, v);
+    } else {
+      lo[e] = x;
+      hi[e] = y;
+    }
+  }
+  __syncthreads();
+
+  // ---- butterflies
+  for (int t = 0; t < p.S; t++) {
+    const int log_h = p.dit ? t : (p.S - 1 - t);
+    const int log_D = log_h + (strided ? log_C : log_cpb);
+    const int log_half = log_h + log_cpb;
+    const int tw_shift = p.log_n - 1 - log_half;
+    const int D = 1 << log_D;
+    for (int bf = threadIdx.x; bf < (tile >> 1); bf += kThreads) {
+      const int w = bf & (D - 1);
+      const int iu = ((bf >> log_D) << (log_D + 1)) + w;
+      const int iv = iu + D;
+      const uint64_t pos = strided ? (((uint64_t)(w >> log_C) << log_cpb) + j0 + (w & (C - 1))) : (uint64_t)w;
+      const Fr tw = ldg_fr(p.tw + (pos << tw_shift));
+      Fr u = ld_fr(lo, hi, iu), v = ld_fr(lo, hi, iv);
+      if (p.dit) {
+        Fr tv = v * tw;
+        st_fr(lo, hi, iu, u + tv);
+        st_fr(lo, hi, iv, u - tv);
+      } else {
+        st_fr(lo, hi, iu, u + v);
+        st_fr(lo, hi, iv, (u - v) * tw);
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- store tile
+  for (int e = threadIdx.x; e < tile; e += kThreads) {
+    uint64_t a = addr_of(e);
+    uint4* g = reinterpret_cast<uint4*>(data + a);
+    if (p.post_tab || p.post_const) {
+      Fr v = ld_fr(lo, hi, e);
+      if (p.post_tab) {
+        uint64_t ti = p.post_bitrev ? bitrev_idx(a, p.log_n) : a;
+        v = v * ldg_fr(p.post_tab + ti);
+      } else {
+        v = v * p.post_c;
+      }
+      g[0] = make_uint4(v.v[0], v.v[1], v.v[2], v.v[3]);
+      g[1] = make_uint4(v.v[4], v.v[5], v.v[6], v.v[7]);
+    } else {
+      g[0] = lo[e];
+      g[1] = hi[e];
+    }
+  }
+}
+
+__global__ void bitrev_permute_kernel(Fr* data, int log_n) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (1ull << log_n)) return;
+  uint64_t j = bitrev_idx(i, log_n);
+  if (i < j) {
+    uint4* a = reinterpret_cast<uint4*>(data + i);
+    uint4* b = reinterpret_cast<uint4*>(data + j);
+    uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
+    a[0] = b0; a[1] = b1; b[0] = a0; b[1] = a1;
+  }
+}
+
+__global__ void scale_table_kernel(Fr* data, uint64_t n, const Fr* tab, Fr c, int use_c) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  data[i] = use_c ? data[i] * c : data[i] * tab[i];
+}
+
+// ---------------------------------------------------------------------------- host side
+static Fr host_fr_from_u64(uint64_t x) {
+  Fr a = Fr::zero();
+  a.v[0] = (uint32_t)x;
+  a.v[1] = (uint32_t)(x >> 32);
+  return a.to_mont();
+}
+static Fr host_root_of_unity(int log_n) {
+  // ark-bls12-381 FrParameters::TWO_ADIC_ROOT_OF_UNITY = 7^((r-1)/2^32), canonical limbs
+  static const uint32_t root[8] = {0x439f0d2bu, 0x3829971fu, 0x8c2280b9u, 0xb6368350u, 0x22c813b4u, 0xd09b6819u, 0xdfe81f20u, 0x16a2a19eu};
+  Fr w;
+  for (int i = 0; i < 8; i++) w.v[i] = root[i];
+  w = w.to_mont();
+  for (int i = log_n; i < 32; i++) w = w.sqr();
+  return w;
+}
+static Fr host_pow_u64(Fr b, uint64_t e) {
+  Fr acc = Fr::one();
+  for (int i = 63; i >= 0; i--) {
+    acc = acc.sqr();
+    if ((e >> i) & 1) acc = acc * b;
+  }
+  return acc;
+}
+
+static int32_t fill_pow_table(ctg_ctx* ctx, Fr* d_out, uint64_t n, Fr base, Fr scale, cudaStream_t st) {
+  if (n == 0) return CTG_OK;
+  PowParams pp;
+  Fr b = base;
+  for (int j = 0; j < 32; j++) { pp.sq[j] = b; b = b.sqr(); }
+  unsigned blocks = (unsigned)((n + 255) / 256);
+  pow_table_kernel<<<blocks, 256, 0, st>>>(d_out, n, pp, scale);
+  CTG_KERNEL_CHECK(ctx);
+  return CTG_OK;
+}
+
+int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
+  if (log_n < 0 || log_n > 28) return fail(ctx, CTG_ERR_INVALID, "ntt: log_n out of range [0, 28]");
+  auto it = ctx->domains.find(log_n);
+  if (it != ctx->domains.end()) { *out = &it->second; return CTG_OK; }
+  NttDomain d;
+  d.log_n = log_n;
+  const uint64_t n = 1ull << log_n;
+  const uint64_t half = n > 1 ? n / 2 : 1;
+  Fr w = host_root_of_unity(log_n), wi = w.inv();
+  Fr g = host_fr_from_u64(7), gi = g.inv();
+  d.n_inv = host_fr_from_u64(n).inv();
+  d.zinv = (host_pow_u64(g, n) - Fr::one()).inv();
+  CTG_CUDA(ctx, cudaMalloc(&d.tw_fwd, half * sizeof(Fr)));
+  CTG_CUDA(ctx, cudaMalloc(&d.tw_inv, half * sizeof(Fr)));
+  CTG_CUDA(ctx, cudaMalloc(&d.gpow, n * sizeof(Fr)));
+  CTG_CUDA(ctx, cudaMalloc(&d.gpow_n, n * sizeof(Fr)));
+  CTG_CUDA(ctx, cudaMalloc(&d.gipow_n, n * sizeof(Fr)));
+  cudaStream_t st = ctx->stream;
+  CTG_TRY(fill_pow_table(ctx, d.tw_fwd, half, w, Fr::one(), st));
+  CTG_TRY(fill_pow_table(ctx, d.tw_inv, half, wi, Fr::one(), st));
+  CTG_TRY(fill_pow_table(ctx, d.gpow, n, g, Fr::one(), st));
+  CTG_TRY(fill_pow_table(ctx, d.gpow_n, n, g, d.n_inv, st));
+  CTG_TRY(fill_pow_table(ctx, d.gipow_n, n, gi, d.n_inv, st));
+  static bool attr_set = false;
+  if (!attr_set) {
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32));
+    attr_set = true;
+  }
+  ctx->domains[log_n] = d;
+  *out = &ctx->domains[log_n];
+  return CTG_OK;
+}
+
+struct PassGeom { int log_blk, S; };
+// DIF order (large sub-transforms first).  DIT uses the same list reversed.
+static std::vector<PassGeom> plan_passes(int log_n) {
+  std::vector<PassGeom> v;
+  int rem = log_n;
+  while (rem > kTileLog) { v.push_back({rem, kStridedLevels}); rem -= kStridedLevels; }
+  if (rem > 0) v.push_back({rem, rem});
+  return v;
+}
+
+struct Fuse {
+  const Fr* pre_tab = nullptr; int pre_bitrev = 0;
+  const Fr* post_tab = nullptr; int post_bitrev = 0;
+  bool post_const = false; Fr post_c;
+};
+
+// Runs all passes of one transform.  dit = 0: natural -> bit-reversed; dit = 1: the reverse.
+static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit, const Fuse& f, cudaStream_t st) {
+  std::vector<PassGeom> plan = plan_passes(log_n);
+  if (dit) std::reverse(plan.begin(), plan.end());
+  const uint64_t n = 1ull << log_n;
+  if (plan.empty()) {  // n == 1: only the scale factors act
+    if (f.pre_tab) { scale_table_kernel<<<1, 32, 0, st>>>(d, 1, f.pre_tab, Fr::one(), 0); CTG_KERNEL_CHECK(ctx); }
+    if (f.post_tab) { scale_table_kernel<<<1, 32, 0, st>>>(d, 1, f.post_tab, Fr::one(), 0); CTG_KERNEL_CHECK(ctx); }
+    if (f.post_const) { scale_table_kernel<<<1, 32, 0, st>>>(d, 1, nullptr, f.post_c, 1); CTG_KERNEL_CHECK(ctx); }
+    return CTG_OK;
+  }
+  for (size_t i = 0; i < plan.size(); i++) {
+    NttPass p;
+    p.log_n = log_n;
+    p.log_blk = plan[i].log_blk;
+    p.S = plan[i].S;
+    p.log_tile = log_n < kTileLog ? log_n : kTileLog;
+    p.dit = dit;
+    p.tw = tw;
+    const bool first = i == 0, last = i + 1 == plan.size();
+    p.pre_tab = first ? f.pre_tab : nullptr;
+    p.pre_bitrev = f.pre_bitrev;
+    p.post_tab = last ? f.post_tab : nullptr;
+    p.post_bitrev = f.post_bitrev;
+    p.post_const = last && f.post_const;
+    p.post_c = f.post_c;
+    unsigned blocks = (unsigned)(n >> p.log_tile);
+    size_t smem = ((size_t)1 << p.log_tile) * 32;
+    ntt_pass_kernel<<<blocks, kThreads, smem, st>>>(d, p);
+    CTG_KERNEL_CHECK(ctx);
+  }
+  return CTG_OK;
+}
+
+int32_t ntt_run(ctg_ctx* ctx, Fr* d, int log_n, int inverse, int coset, cudaStream_t st) {
+  NttDomain* dom;
+  CTG_TRY(ntt_get_domain(ctx, log_n, &dom));
+  Fuse f;
+  if (!inverse) {
+    if (coset) f.pre_tab = dom->gpow;  // x_i * g^i on the natural-order input
+    CTG_TRY(run_passes(ctx, d, log_n, dom->tw_fwd, 0, f, st));
+  } else {
+    if (coset) { f.post_tab = dom->gipow_n; f.post_bitrev = 1; }  // output still bit-reversed here
+    else { f.post_const = true; f.post_c = dom->n_inv; }
+    CTG_TRY(run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st));
+  }
+  if (log_n > 1) {
+    uint64_t n = 1ull << log_n;
+    bitrev_permute_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, log_n);
+    CTG_KERNEL_CHECK(ctx);
+  }
+  return CTG_OK;
+}
+
+int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d, int log_n, cudaStream_t st) {
+  NttDomain* dom;
+  CTG_TRY(ntt_get_domain(ctx, log_n, &dom));
+  Fuse f;
+  f.post_tab = dom->gpow_n;  // (1/n) * g^i, i = natural index of the bit-reversed slot
+  f.post_bitrev = 1;
+  CTG_TRY(run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st));
+  Fuse none;
+  return run_passes(ctx, d, log_n, dom->tw_fwd, 1, none, st);
+}
+
+int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d, int log_n, cudaStream_t st) {
+  NttDomain* dom;
+  CTG_TRY(ntt_get_domain(ctx, log_n, &dom));
+  Fuse f;
+  f.post_tab = dom->gipow_n;
+  f.post_bitrev = 1;
+  return run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st);
+}
+
+}  // namespace ctg

@@ -1,0 +1,319 @@
+"""ctypes binding of libctg_groth16.so (include/ctg_groth16.h) -- the harness tests/ and
+bench.py drive the C ABI through; a thin mirror of what the Rust `ctg-groth16-sys` crate
+binds.  There is no CPU path here: importing works anywhere (so the CPU
+test-suite can check that the library loads and exports its symbols), but every compute
+call needs a CUDA device and raises CtgError otherwise.
+
+Arrays are numpy uint32 in the wire layout of the header: Fr (n, 8), Fq (n, 12),
+G1 affine (n, 24), G2 affine (n, 48), Montgomery limbs, all-zero = point at infinity.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libctg_groth16.so")
+
+FR_W, FQ_W, G1_W, G2_W = 8, 12, 24, 48
+SCALARS_CANONICAL, SCALARS_MONT, MSM_TIMED = 0, 1, 0x100
+FIELD_FR, FIELD_FQ, FIELD_FQ2 = 0, 1, 2
+OP_MUL, OP_ADD, OP_SUB = 0, 1, 2
+
+# every symbol include/ctg_groth16.h declares (checked by tests/test_abi_cpu.py)
+EXPORTS = [
+    "ctg_ctx_create", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_sync", "ctg_launch_count",
+    "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch",
+    "ctg_fr_mul_batch", "ctg_fq_mul_batch", "ctg_imad_peak_probe", "ctg_ntt_fr", "ctg_ntt_fr_dev",
+    "ctg_bases_upload_g1", "ctg_bases_upload_g2", "ctg_bases_progression_g1", "ctg_bases_progression_g2",
+    "ctg_bases_download", "ctg_bases_free", "ctg_bases_len", "ctg_msm_g1", "ctg_msm_g2", "ctg_msm_g1_dev",
+    "ctg_msm_g2_dev", "ctg_msm_g1_partial", "ctg_msm_g2_partial", "ctg_g1_combine", "ctg_g2_combine",
+    "ctg_g1_combine_dev", "ctg_g2_combine_dev", "ctg_pk_upload", "ctg_pk_free", "ctg_r1cs_upload",
+    "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch",
+]
+
+
+class CtgError(RuntimeError):
+    pass
+
+
+class PkView(C.Structure):
+    _fields_ = [("alpha_g1", C.c_void_p), ("beta_g1", C.c_void_p), ("delta_g1", C.c_void_p),
+                ("beta_g2", C.c_void_p), ("delta_g2", C.c_void_p),
+                ("a_query", C.c_void_p), ("a_len", C.c_uint64),
+                ("b_g1_query", C.c_void_p), ("b_g1_len", C.c_uint64),
+                ("b_g2_query", C.c_void_p), ("b_g2_len", C.c_uint64),
+                ("h_query", C.c_void_p), ("h_len", C.c_uint64),
+                ("l_query", C.c_void_p), ("l_len", C.c_uint64)]
+
+
+class Csr(C.Structure):
+    _fields_ = [("row_ptr", C.c_void_p), ("col", C.c_void_p), ("val", C.c_void_p)]
+
+
+class Timings(C.Structure):
+    _fields_ = [(k, C.c_float) for k in ("h2d_ms", "witness_map_ms", "msm_h_ms", "msm_l_ms", "msm_a_ms", "msm_b_g1_ms",
+                                         "msm_b_g2_ms", "finalize_ms", "total_ms", "msm_sort_ms", "msm_accumulate_ms",
+                                         "msm_reduce_ms")]
+
+    def as_dict(self):
+        return {k: float(getattr(self, k)) for k, _ in self._fields_}
+
+
+_lib = None
+
+
+def load():
+    """Load the CUDA extension; fail loudly if it was not built (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise CtgError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C contangle-zkcp_b200/csrc). There is no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        lib.ctg_last_error.restype = C.c_char_p
+        lib.ctg_launch_count.restype = C.c_uint64
+        lib.ctg_bases_len.restype = C.c_uint64
+        for name in ("ctg_ctx_destroy", "ctg_bases_free", "ctg_pk_free", "ctg_r1cs_free"):
+            getattr(lib, name).restype = None
+        _lib = lib
+    return _lib
+
+
+def _arr(a, words=None):
+    a = np.ascontiguousarray(a, dtype=np.uint32)
+    if words is not None and (a.ndim == 0 or a.shape[-1] != words):
+        raise CtgError(f"expected trailing dimension {words}, got shape {a.shape}")
+    return a
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+class Bases:
+    def __init__(self, ctx, handle, group):
+        self.ctx, self.handle, self.group = ctx, handle, group
+
+    def __len__(self):
+        return int(load().ctg_bases_len(self.handle))
+
+    def download(self, first=0, count=None):
+        count = len(self) - first if count is None else count
+        out = np.zeros((count, G1_W if self.group == 1 else G2_W), dtype=np.uint32)
+        self.ctx._check(load().ctg_bases_download(self.ctx.h, self.handle, C.c_uint64(first), C.c_uint64(count), _ptr(out)))
+        return out
+
+    def free(self):
+        if self.handle:
+            load().ctg_bases_free(self.ctx.h, self.handle)
+            self.handle = None
+
+
+class Context:
+    """One CUDA device (ctg_ctx).  `stream`: a raw cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+
+    def __init__(self, device=0, stream=None):
+        lib = load()
+        self.h = C.c_void_p()
+        ids = (C.c_int * 1)(device)
+        rc = lib.ctg_ctx_create(ids, 1, C.byref(self.h))
+        if rc != 0:
+            raise CtgError(f"ctg_ctx_create failed with {rc}: no usable sm_100 CUDA device (there is no CPU fallback)")
+        if stream is not None:
+            self._check(lib.ctg_ctx_set_stream(self.h, C.c_void_p(stream)))
+
+    def _check(self, rc):
+        if rc != 0:
+            raise CtgError(f"ctg error {rc}: {load().ctg_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            load().ctg_ctx_destroy(self.h)
+            self.h = None
+
+    def sync(self):
+        self._check(load().ctg_sync(self.h))
+
+    @property
+    def launches(self):
+        return int(load().ctg_launch_count(self.h))
+
+    def last_timings(self):
+        t = Timings()
+        self._check(load().ctg_last_timings(self.h, C.byref(t)))
+        return t.as_dict()
+
+    # ---- fields
+    def field_op(self, field, op, a, b):
+        w = {FIELD_FR: FR_W, FIELD_FQ: FQ_W, FIELD_FQ2: 2 * FQ_W}[field]
+        a, b = _arr(a, w), _arr(b, w)
+        out = np.empty_like(a)
+        self._check(load().ctg_field_op_batch(self.h, field, op, _ptr(a), _ptr(b), _ptr(out), C.c_size_t(a.shape[0])))
+        return out
+
+    def fr_mul(self, a, b):
+        a, b = _arr(a, FR_W), _arr(b, FR_W)
+        out = np.empty_like(a)
+        self._check(load().ctg_fr_mul_batch(self.h, _ptr(a), _ptr(b), _ptr(out), C.c_size_t(a.shape[0])))
+        return out
+
+    def fq_mul(self, a, b):
+        a, b = _arr(a, FQ_W), _arr(b, FQ_W)
+        out = np.empty_like(a)
+        self._check(load().ctg_fq_mul_batch(self.h, _ptr(a), _ptr(b), _ptr(out), C.c_size_t(a.shape[0])))
+        return out
+
+    def imad_peak_probe(self):
+        imad, fq = C.c_double(), C.c_double()
+        self._check(load().ctg_imad_peak_probe(self.h, C.byref(imad), C.byref(fq)))
+        return imad.value, fq.value
+
+    # ---- NTT
+    def ntt(self, data, inverse=False, coset=False):
+        data = _arr(data, FR_W).copy()
+        n = data.shape[0]
+        log_n = n.bit_length() - 1
+        if n == 0 or (1 << log_n) != n:
+            raise CtgError("ntt: length must be a power of two")
+        self._check(load().ctg_ntt_fr(self.h, _ptr(data), C.c_uint32(log_n), int(inverse), int(coset)))
+        return data
+
+    def ntt_dev(self, d_ptr, log_n, inverse=False, coset=False):
+        self._check(load().ctg_ntt_fr_dev(self.h, C.c_void_p(d_ptr), C.c_uint32(log_n), int(inverse), int(coset)))
+
+    # ---- bases / MSM
+    def bases_g1(self, points, copies=1, c_bits=0):
+        points = _arr(points, G1_W)
+        h = C.c_void_p()
+        self._check(load().ctg_bases_upload_g1(self.h, _ptr(points), C.c_uint64(points.shape[0]), copies, c_bits, C.byref(h)))
+        return Bases(self, h, 1)
+
+    def bases_g2(self, points, copies=1, c_bits=0):
+        points = _arr(points, G2_W)
+        h = C.c_void_p()
+        self._check(load().ctg_bases_upload_g2(self.h, _ptr(points), C.c_uint64(points.shape[0]), copies, c_bits, C.byref(h)))
+        return Bases(self, h, 2)
+
+    def bases_progression_g1(self, g, a_mont, b_mont, n, copies=1, c_bits=0):
+        g, a_mont, b_mont = _arr(g).reshape(G1_W), _arr(a_mont).reshape(FR_W), _arr(b_mont).reshape(FR_W)
+        h = C.c_void_p()
+        self._check(load().ctg_bases_progression_g1(self.h, _ptr(g), _ptr(a_mont), _ptr(b_mont), C.c_uint64(n), copies, c_bits, C.byref(h)))
+        return Bases(self, h, 1)
+
+    def bases_progression_g2(self, g, a_mont, b_mont, n, copies=1, c_bits=0):
+        g, a_mont, b_mont = _arr(g).reshape(G2_W), _arr(a_mont).reshape(FR_W), _arr(b_mont).reshape(FR_W)
+        h = C.c_void_p()
+        self._check(load().ctg_bases_progression_g2(self.h, _ptr(g), _ptr(a_mont), _ptr(b_mont), C.c_uint64(n), copies, c_bits, C.byref(h)))
+        return Bases(self, h, 2)
+
+    def msm(self, bases: Bases, scalars, mont=False, n=None, timed=False):
+        """sum_i scalars[i] * bases[i] -> affine point (24 or 48 words).  Scalars are host memory."""
+        scalars = _arr(scalars, FR_W)
+        n = scalars.shape[0] if n is None else n
+        flags = (SCALARS_MONT if mont else 0) | (MSM_TIMED if timed else 0)
+        out = np.zeros(G1_W if bases.group == 1 else G2_W, dtype=np.uint32)
+        fn = load().ctg_msm_g1 if bases.group == 1 else load().ctg_msm_g2
+        self._check(fn(self.h, bases.handle, _ptr(scalars), C.c_uint64(n), C.c_uint32(flags), _ptr(out)))
+        return out
+
+    def msm_dev(self, bases: Bases, d_scalars, n, d_out_xyzz, mont=False, timed=False):
+        flags = (SCALARS_MONT if mont else 0) | (MSM_TIMED if timed else 0)
+        fn = load().ctg_msm_g1_dev if bases.group == 1 else load().ctg_msm_g2_dev
+        self._check(fn(self.h, bases.handle, C.c_void_p(d_scalars), C.c_uint64(n), C.c_uint32(flags), C.c_void_p(d_out_xyzz)))
+
+    def msm_partial(self, bases: Bases, scalars, mont=False):
+        scalars = _arr(scalars, FR_W)
+        out = np.zeros(2 * (G1_W if bases.group == 1 else G2_W), dtype=np.uint32)
+        fn = load().ctg_msm_g1_partial if bases.group == 1 else load().ctg_msm_g2_partial
+        self._check(fn(self.h, bases.handle, _ptr(scalars), C.c_uint64(scalars.shape[0]), C.c_uint32(SCALARS_MONT if mont else 0), _ptr(out)))
+        return out
+
+    def combine(self, partials, group=1):
+        w = 2 * (G1_W if group == 1 else G2_W)
+        partials = _arr(partials, w)
+        out = np.zeros(G1_W if group == 1 else G2_W, dtype=np.uint32)
+        fn = load().ctg_g1_combine if group == 1 else load().ctg_g2_combine
+        self._check(fn(self.h, _ptr(partials), C.c_uint32(partials.shape[0]), _ptr(out)))
+        return out
+
+    def combine_dev(self, d_partials, k, d_out_affine, group=1):
+        fn = load().ctg_g1_combine_dev if group == 1 else load().ctg_g2_combine_dev
+        self._check(fn(self.h, C.c_void_p(d_partials), C.c_uint32(k), C.c_void_p(d_out_affine)))
+
+    # ---- proving key / R1CS / prover
+    def upload_pk(self, pk: dict, num_instance, num_constraints, copies=1, c_bits=0):
+        """pk: dict of arrays alpha_g1, beta_g1, delta_g1, beta_g2, delta_g2, a_query, b_g1_query, b_g2_query, h_query, l_query."""
+        v = PkView()
+        keep = []
+        for k, w in (("alpha_g1", G1_W), ("beta_g1", G1_W), ("delta_g1", G1_W), ("beta_g2", G2_W), ("delta_g2", G2_W)):
+            a = _arr(pk[k]).reshape(w); keep.append(a); setattr(v, k, a.ctypes.data)
+        for k, w in (("a_query", G1_W), ("b_g1_query", G1_W), ("b_g2_query", G2_W), ("h_query", G1_W), ("l_query", G1_W)):
+            a = _arr(pk[k]).reshape(-1, w); keep.append(a); setattr(v, k, a.ctypes.data)
+            setattr(v, k.replace("_query", "_len"), a.shape[0])
+        h = C.c_void_p()
+        self._check(load().ctg_pk_upload(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits, C.byref(h)))
+        return DevicePk(self, h, pk["a_query"].shape[0])
+
+    def upload_r1cs(self, r1cs: dict):
+        mats, keep = [], []
+        for k in "abc":
+            m = r1cs[k]
+            rp = np.ascontiguousarray(m["row_ptr"], dtype=np.uint64)
+            col = np.ascontiguousarray(m["col"], dtype=np.uint32)
+            val = _arr(m["val"]).reshape(-1, FR_W)
+            keep += [rp, col, val]
+            mats.append(Csr(rp.ctypes.data, col.ctypes.data, val.ctypes.data))
+        h = C.c_void_p()
+        self._check(load().ctg_r1cs_upload(self.h, C.c_uint64(r1cs["num_instance"]), C.c_uint64(r1cs["num_witness"]),
+                                           C.c_uint64(r1cs["num_constraints"]), C.byref(mats[0]), C.byref(mats[1]), C.byref(mats[2]), C.byref(h)))
+        n = 1
+        while n < r1cs["num_instance"] + r1cs["num_constraints"]:
+            n *= 2
+        return DeviceR1cs(self, h, r1cs["num_instance"] + r1cs["num_witness"], n)
+
+    def witness_map(self, r1cs: "DeviceR1cs", z):
+        z = _arr(z, FR_W)
+        if z.shape[0] != r1cs.m:
+            raise CtgError("witness_map: assignment length differs from num_instance + num_witness")
+        h = np.zeros((r1cs.n, FR_W), dtype=np.uint32)
+        self._check(load().ctg_witness_map(self.h, r1cs.handle, _ptr(z), _ptr(h)))
+        return h
+
+    def prove(self, pk: "DevicePk", r1cs: "DeviceR1cs", z, r, s, timed=False):
+        """ark_groth16::create_proof after synthesis.  Returns (A (24,), B (48,), C (24,))[, timings]."""
+        z = _arr(z, FR_W)
+        if z.shape[0] != r1cs.m or pk.m != r1cs.m:
+            raise CtgError("prove: assignment / key / R1CS sizes differ")
+        r, s = _arr(r).reshape(FR_W), _arr(s).reshape(FR_W)
+        out = np.zeros(G1_W + G2_W + G1_W, dtype=np.uint32)
+        t = Timings()
+        self._check(load().ctg_prove(self.h, pk.handle, r1cs.handle, _ptr(z), _ptr(r), _ptr(s), _ptr(out), C.byref(t) if timed else None))
+        proof = (out[:G1_W].copy(), out[G1_W:G1_W + G2_W].copy(), out[G1_W + G2_W:].copy())
+        return (proof, t.as_dict()) if timed else proof
+
+    def prove_ptr(self, pk, r1cs, z_ptr, r, s, out):
+        """Same with a raw host pointer for z (e.g. a pinned torch tensor) and a preallocated output (96 words)."""
+        self._check(load().ctg_prove(self.h, pk.handle, r1cs.handle, C.c_void_p(z_ptr), _ptr(r), _ptr(s), _ptr(out), None))
+
+
+class DevicePk:
+    def __init__(self, ctx, handle, m):
+        self.ctx, self.handle, self.m = ctx, handle, m
+
+    def free(self):
+        if self.handle:
+            load().ctg_pk_free(self.ctx.h, self.handle)
+            self.handle = None
+
+
+class DeviceR1cs:
+    def __init__(self, ctx, handle, m, n):
+        self.ctx, self.handle, self.m, self.n = ctx, handle, m, n
+
+    def free(self):
+        if self.handle:
+            load().ctg_r1cs_free(self.ctx.h, self.handle)
+            self.handle = None

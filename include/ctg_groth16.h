@@ -1,0 +1,188 @@
+/* ctg_groth16.h -- C ABI of libctg_groth16.so, a B200-native (sm_100a) Groth16 proving
+ * backend for BLS12-381.  Drop-in boundary for ONE path of nulltea/contangle-zkcp:
+ *     Groth16::<Bls12_381>::prove(&pk, circuit, rng)
+ * as called at lib/src/zk/encryption.rs:76, lib/src/zk/verifiable_encryption.rs:92,
+ * lib/src/zk/sample_entries.rs:86 and lib/src/zk/property.rs:133, i.e.
+ * ark_groth16::create_random_proof / create_proof (ark-groth16 ^0.3.0, not in the tree;
+ * declared at circuits-ark/Cargo.toml:17).  Constraint synthesis stays on the host
+ * (reference language: Rust); everything from "R1CS matrices + full assignment" to
+ * "affine (A, B, C)" runs on the GPU.  INTEGRATION.md shows the Rust `extern "C"` block
+ * and the safe wrapper a maintainer would add; contangle-zkcp_b200/host/ctg_groth16.hpp
+ * mirrors the ark-groth16 API shape in C++ on top of this header.
+ *
+ * Conventions
+ *  - Plain C, no exceptions cross the boundary.  Every function returns int32_t:
+ *    CTG_OK (0) or a negative CTG_ERR_*; ctg_last_error(ctx) gives the message.
+ *  - Opaque handles.  A context is bound to one CUDA device (one process per GPU);
+ *    handles are thread-compatible: one in-flight call per context.
+ *  - Field elements are little-endian Montgomery limb images with R = 2^256 (Fr) and
+ *    R = 2^384 (Fq): byte-identical to ark-ff 0.3.0 Fp256 / Fp384 ([u64; 4] / [u64; 6]).
+ *    Affine points are x || y; G2 coordinates are c0 || c1.  The point at infinity is the
+ *    all-zero image ((0,0) is not on either curve).  ark-ec's GroupAffine is not repr(C);
+ *    the Rust shim repacks.
+ *  - "host" pointers are caller-owned host memory, copied during the call.  "_dev"
+ *    entry points take device pointers (e.g. torch tensors' data_ptr()).
+ *  - There is no CPU fallback: without a usable CUDA device ctg_ctx_create fails.
+ */
+#ifndef CTG_GROTH16_H
+#define CTG_GROTH16_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTG_OK 0
+#define CTG_ERR_INVALID (-1)
+#define CTG_ERR_CUDA (-2)
+#define CTG_ERR_OOM (-3)
+#define CTG_ERR_STATE (-4)
+
+/* scalar encodings accepted by the MSM entry points */
+#define CTG_SCALARS_CANONICAL 0u /* ark-ff BigInteger256 (into_repr) images, as VariableBaseMSM takes them */
+#define CTG_SCALARS_MONT 1u      /* ark-ff Fr memory images (Montgomery) */
+#define CTG_MSM_TIMED 0x100u      /* record per-stage CUDA-event times (adds one stream sync); read with ctg_last_timings */
+
+typedef struct ctg_ctx ctg_ctx;
+typedef struct ctg_bases ctg_bases; /* device-resident base table (one proving-key query) */
+typedef struct ctg_pk ctg_pk;       /* device-resident proving key (replaces the host ProvingKey cache,
+                                       lib/src/zk/encryption.rs:22,31-32; lib/src/utils.rs:104-110) */
+typedef struct ctg_r1cs ctg_r1cs;   /* device-resident R1CS matrices (ark-relations to_matrices()) */
+
+typedef struct { uint32_t v[8]; } ctg_fr;
+typedef struct { uint32_t v[12]; } ctg_fq;
+typedef struct { ctg_fq x, y; } ctg_g1_affine;                     /* 96 B  */
+typedef struct { ctg_fq x_c0, x_c1, y_c0, y_c1; } ctg_g2_affine;   /* 192 B */
+typedef struct { ctg_fq x, y, zz, zzz; } ctg_g1_xyzz;              /* 192 B, x = X/ZZ, y = Y/ZZZ; ZZ = 0 is infinity */
+typedef struct { ctg_fq c[8]; } ctg_g2_xyzz;                       /* 384 B */
+
+/* ark_groth16::Proof<Bls12_381> { a: G1Affine, b: G2Affine, c: G1Affine } */
+typedef struct { ctg_g1_affine a; ctg_g2_affine b; ctg_g1_affine c; } ctg_proof;
+
+/* ark_groth16::ProvingKey<Bls12_381> as pointers + lengths. */
+typedef struct {
+  const ctg_g1_affine* alpha_g1; /* vk.alpha_g1 */
+  const ctg_g1_affine* beta_g1;
+  const ctg_g1_affine* delta_g1;
+  const ctg_g2_affine* beta_g2;  /* vk.beta_g2 */
+  const ctg_g2_affine* delta_g2; /* vk.delta_g2 */
+  const ctg_g1_affine* a_query;    uint64_t a_len;    /* m = num_instance + num_witness */
+  const ctg_g1_affine* b_g1_query; uint64_t b_g1_len; /* m */
+  const ctg_g2_affine* b_g2_query; uint64_t b_g2_len; /* m */
+  const ctg_g1_affine* h_query;    uint64_t h_len;    /* n - 1 */
+  const ctg_g1_affine* l_query;    uint64_t l_len;    /* num_witness */
+} ctg_pk_view;
+
+/* One R1CS matrix in CSR form.  Columns index z = instance (z[0] = 1) ++ witness. */
+typedef struct {
+  const uint64_t* row_ptr; /* num_constraints + 1 */
+  const uint32_t* col;     /* nnz */
+  const ctg_fr* val;       /* nnz, Montgomery */
+} ctg_csr;
+
+/* Per-stage device times (ms) of the last ctg_prove / ctg_msm_* call, CUDA events on the
+ * context's stream.  Stage names follow arkworks' start_timer! spans. */
+typedef struct {
+  float h2d_ms;          /* assignment upload */
+  float witness_map_ms;  /* "R1CS to QAP witness map": SpMV + 7 NTT + pointwise */
+  float msm_h_ms, msm_l_ms, msm_a_ms, msm_b_g1_ms, msm_b_g2_ms;
+  float finalize_ms;     /* s*A + r*B1 + ..., to_affine, D2H */
+  float total_ms;
+  /* inside the last MSM: */
+  float msm_sort_ms;       /* digit recode + bucket counting sort */
+  float msm_accumulate_ms; /* bucket accumulation (dominant kernel) */
+  float msm_reduce_ms;     /* bucket-sum reduction + window combine */
+} ctg_timings;
+
+/* ---- context ---------------------------------------------------------------------- */
+/* One device per context: n_devices must be 1 (multi-GPU runs use one process / context per
+ * GPU and exchange 192-byte partial sums, see ctg_msm_g1_partial + ctg_g1_combine). */
+int32_t ctg_ctx_create(const int* device_ids, int n_devices, ctg_ctx** out);
+void ctg_ctx_destroy(ctg_ctx* ctx);
+const char* ctg_last_error(ctg_ctx* ctx);
+/* Run all work of this context on a caller-owned cudaStream_t (e.g. torch's current stream). */
+int32_t ctg_ctx_set_stream(ctg_ctx* ctx, void* cuda_stream);
+int32_t ctg_sync(ctg_ctx* ctx);
+uint64_t ctg_launch_count(ctg_ctx* ctx); /* kernels launched by this context so far */
+int32_t ctg_last_timings(ctg_ctx* ctx, ctg_timings* out);
+
+/* ---- device memory helpers (for callers that do not own a CUDA allocator) ----------- */
+int32_t ctg_dev_alloc(ctg_ctx* ctx, size_t bytes, void** d_out);
+int32_t ctg_dev_free(ctg_ctx* ctx, void* d_ptr);
+int32_t ctg_h2d(ctg_ctx* ctx, void* d_dst, const void* h_src, size_t bytes);
+int32_t ctg_d2h(ctg_ctx* ctx, void* h_dst, const void* d_src, size_t bytes);
+
+/* ---- field kernels (replaces ark-ff Fp256/Fp384 mul_assign/add_assign/sub_assign; used by
+ *      tests and the ncu integer-pipe captures) --------------------------------------- */
+#define CTG_FIELD_FR 0
+#define CTG_FIELD_FQ 1
+#define CTG_FIELD_FQ2 2
+#define CTG_OP_MUL 0
+#define CTG_OP_ADD 1
+#define CTG_OP_SUB 2
+/* out[i] = a[i] (op) b[i]; host buffers of n elements (32 / 48 / 96 bytes each) */
+int32_t ctg_field_op_batch(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n);
+int32_t ctg_fr_mul_batch(ctg_ctx* ctx, const ctg_fr* a, const ctg_fr* b, ctg_fr* out, size_t n);
+int32_t ctg_fq_mul_batch(ctg_ctx* ctx, const ctg_fq* a, const ctg_fq* b, ctg_fq* out, size_t n);
+/* Measured integer-pipe peaks of this GPU: IMAD (32-bit) instructions/s over all SMs, and the
+ * sustained rate of dependent Fq Montgomery products (300 MAC32 each). */
+int32_t ctg_imad_peak_probe(ctg_ctx* ctx, double* imad_per_s, double* fq_mul_per_s);
+
+/* ---- NTT (replaces ark-poly 0.3.0 Radix2EvaluationDomain::{fft,ifft,coset_fft,coset_ifft}_in_place
+ *      over Fr; natural order in, natural order out; ifft scales by 1/n; coset shift g = 7) */
+int32_t ctg_ntt_fr(ctg_ctx* ctx, ctg_fr* host_data, uint32_t log_n, int inverse, int coset);
+int32_t ctg_ntt_fr_dev(ctg_ctx* ctx, void* d_data, uint32_t log_n, int inverse, int coset);
+
+/* ---- base tables and MSM (replaces ark-ec 0.3.0 VariableBaseMSM::multi_scalar_mul) ---- */
+/* copies >= 1: keep 2^(c*G*j) * P for j < copies in HBM so that only G = ceil(W/copies) bucket
+ * sets are reduced (0 = let the library choose); c_bits = 0 lets the library choose. */
+int32_t ctg_bases_upload_g1(ctg_ctx* ctx, const ctg_g1_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out);
+int32_t ctg_bases_upload_g2(ctg_ctx* ctx, const ctg_g2_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out);
+/* synthetic tables generated on the device: P_i = (a + i*b) * g  (distinct subgroup points with known dlogs) */
+int32_t ctg_bases_progression_g1(ctg_ctx* ctx, const ctg_g1_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out);
+int32_t ctg_bases_progression_g2(ctg_ctx* ctx, const ctg_g2_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out);
+int32_t ctg_bases_download(ctg_ctx* ctx, const ctg_bases* bases, uint64_t first, uint64_t count, void* host_points);
+void ctg_bases_free(ctg_ctx* ctx, ctg_bases* bases);
+uint64_t ctg_bases_len(const ctg_bases* bases);
+
+/* sum_{i<n} scalars[i] * bases[i], n <= len(bases); affine result in host memory */
+int32_t ctg_msm_g1(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_affine* out);
+int32_t ctg_msm_g2(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g2_affine* out);
+/* scalars already in HBM; d_out_xyzz (device, 192 / 384 B) receives the projective sum; no host sync */
+int32_t ctg_msm_g1_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz);
+int32_t ctg_msm_g2_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz);
+/* multi-GPU: each rank runs the MSM over its point range and returns the projective partial sum;
+ * the partials are gathered (NCCL all_gather of 192 B per rank) and combined on one rank. */
+int32_t ctg_msm_g1_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_xyzz* out);
+int32_t ctg_msm_g2_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g2_xyzz* out);
+int32_t ctg_g1_combine(ctg_ctx* ctx, const ctg_g1_xyzz* host_partials, uint32_t k, ctg_g1_affine* out);
+int32_t ctg_g2_combine(ctg_ctx* ctx, const ctg_g2_xyzz* host_partials, uint32_t k, ctg_g2_affine* out);
+int32_t ctg_g1_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine);
+int32_t ctg_g2_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine);
+
+/* ---- proving key / R1CS caches and the prover ---------------------------------------- */
+/* copies / c_bits as for ctg_bases_upload_* (applied to every query). */
+int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits, ctg_pk** out);
+void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk);
+int32_t ctg_r1cs_upload(ctg_ctx* ctx, uint64_t num_instance, uint64_t num_witness, uint64_t num_constraints, const ctg_csr* a,
+                        const ctg_csr* b, const ctg_csr* c, ctg_r1cs** out);
+void ctg_r1cs_free(ctg_ctx* ctx, ctg_r1cs* r1cs);
+
+/* ark_groth16 R1CStoQAP::witness_map: h_out receives n = next_pow2(num_constraints + num_instance)
+ * coefficients in natural order (host). */
+int32_t ctg_witness_map(ctg_ctx* ctx, const ctg_r1cs* r1cs, const ctg_fr* z, ctg_fr* h_out);
+
+/* ark_groth16::create_proof(circuit, pk, r, s) after synthesis: z = instance ++ witness
+ * (m elements, z[0] = 1, Montgomery), r and s drawn by the caller (Fr::rand, r first). */
+int32_t ctg_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
+                  ctg_proof* out, ctg_timings* timings /* may be NULL */);
+/* n_proofs independent assignments (z_batch: n_proofs * m), rs_batch: n_proofs * 2 (r, s) */
+int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, uint32_t n_proofs, const ctg_fr* z_batch,
+                        const ctg_fr* rs_batch, ctg_proof* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTG_GROTH16_H */

@@ -1,0 +1,131 @@
+"""CPU tests of the DEVICE field/curve headers compiled for the host (csrc/ptx.cuh emulates
+the PTX carry chain): the exact mont_mul / XYZZ code the kernels run, against the oracle."""
+import ctypes as C
+import os
+import random
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import ark
+from oracle.py import bls12_381 as B
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+rnd = random.Random(99)
+
+
+@pytest.fixture(scope="module")
+def hm():
+    subprocess.check_call(["make", "-C", os.path.join(HERE, "host_math")], stdout=subprocess.DEVNULL)
+    return C.CDLL(os.path.join(HERE, "host_math", "libhost_math.so"))
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _edge(mod, n):
+    vals = [0, 1, 2, mod - 1, mod - 2, (1 << 255) % mod, (mod - 1) // 2, 0xFFFFFFFF, 1 << 32, (1 << 64) - 1]
+    vals += [rnd.randrange(mod) for _ in range(n)]
+    return vals
+
+
+@pytest.mark.parametrize("field", ["fr", "fq"])
+def test_field_ops_match_oracle(hm, field):
+    mod, w = (B.R_MOD, 8) if field == "fr" else (B.P_MOD, 12)
+    av = _edge(mod, 500)
+    bv = list(reversed(_edge(mod, 500)))
+    # Montgomery images straight from ints (x*R mod p) -- any value < p is a valid image
+    a = ark.ints_to_words(av, w)
+    b = ark.ints_to_words(bv, w)
+    for op in ("mul", "add", "sub"):
+        out = np.zeros_like(a)
+        getattr(hm, f"hm_{field}_{op}")(_p(a), _p(b), _p(out), C.c_uint64(len(av)))
+        want = getattr(ark, f"{field}_{op}")(a, b)
+        assert np.array_equal(out, want), op
+
+
+def test_fr_mont_conversions(hm):
+    vals = _edge(B.R_MOD, 50)
+    a = ark.ints_to_words(vals, 8)
+    out = np.zeros_like(a)
+    hm.hm_fr_to_mont(_p(a), _p(out), C.c_uint64(len(vals)))
+    assert np.array_equal(out, ark.fr_to_mont(a))
+    back = np.zeros_like(a)
+    hm.hm_fr_from_mont(_p(out), _p(back), C.c_uint64(len(vals)))
+    assert np.array_equal(back, a)
+
+
+def test_fq2_and_inverse(hm):
+    n = 40
+    a = ark.ints_to_words([rnd.randrange(B.P_MOD) for _ in range(2 * n)], 12).reshape(n, 24)
+    b = ark.ints_to_words([rnd.randrange(B.P_MOD) for _ in range(2 * n)], 12).reshape(n, 24)
+    out = np.zeros_like(a)
+    hm.hm_fq2_mul(_p(a), _p(b), _p(out), C.c_uint64(n))
+    assert np.array_equal(out, ark.fq2_mul(a, b))
+    hm.hm_fq2_sqr(_p(a), _p(out), C.c_uint64(n))
+    assert np.array_equal(out, ark.fq2_mul(a, a))
+    x = a.reshape(-1, 12)[:8].copy()
+    inv = np.zeros_like(x)
+    hm.hm_fq_inv(_p(x), _p(inv), C.c_uint64(8))
+    one = ark.fq_to_mont(ark.ints_to_words([1] * 8, 12))
+    assert np.array_equal(ark.fq_mul(x, inv), one)
+
+
+def test_xyzz_sum_with_special_cases(hm):
+    a, b = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    n = 24
+    fm = lambda v: ark.fr_mont_from_ints([v])[0]
+    pts = ark.g1_progression(ark.g1_generator(), fm(a), fm(b), n)
+    dl = [(a + i * b) % B.R_MOD for i in range(n)]
+    # duplicates (forces the doubling path), an inverse pair (P + -P), identity points
+    pts[1] = pts[0]; dl[1] = dl[0]
+    pts[7] = 0; dl[7] = 0
+    neg = np.zeros(n, dtype=np.uint8)
+    neg[3] = 1; dl[3] = -dl[3]
+    pts[10] = pts[9]; neg[10] = 1; dl[10] = -dl[9]
+    out = np.zeros(24, dtype=np.uint32)
+    hm.hm_g1_sum(_p(pts), _p(neg), C.c_uint64(n), _p(out))
+    assert ark.g1_to_py(out)[0] == B.G1.mul(B.G1_GEN, sum(dl) % B.R_MOD)
+    # cancel to infinity: P, P, -P, -P
+    four = np.stack([pts[0]] * 4)
+    hm.hm_g1_sum(_p(four), _p(np.array([0, 0, 1, 1], dtype=np.uint8)), C.c_uint64(4), _p(out))
+    assert not out.any()
+    # G2
+    p2 = ark.g2_progression(ark.g2_generator(), fm(a), fm(b), 8)
+    p2[2] = p2[1]
+    out2 = np.zeros(48, dtype=np.uint32)
+    hm.hm_g2_sum(_p(p2), _p(np.zeros(8, dtype=np.uint8)), C.c_uint64(8), _p(out2))
+    d2 = [(a + i * b) for i in range(8)]; d2[2] = d2[1]
+    assert ark.g2_to_py(out2)[0] == B.G2.mul(B.G2_GEN, sum(d2) % B.R_MOD)
+
+
+def test_xyzz_full_add_tree_and_scalar_mul(hm):
+    a, b = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    fm = lambda v: ark.fr_mont_from_ints([v])[0]
+    pts = ark.g1_progression(ark.g1_generator(), fm(a), fm(b), 16)
+    pts[4] = pts[5]  # equal operands in the first tree level -> xyzz_add doubling path
+    pts[8] = 0
+    out = np.zeros(24, dtype=np.uint32)
+    hm.hm_g1_tree(_p(pts), C.c_uint64(16), _p(out))
+    dl = [(a + i * b) for i in range(16)]; dl[4] = dl[5]; dl[8] = 0
+    assert ark.g1_to_py(out)[0] == B.G1.mul(B.G1_GEN, sum(dl) % B.R_MOD)
+    for k in (0, 1, 2, B.R_MOD - 1, rnd.randrange(B.R_MOD)):
+        kc = ark.ints_to_words([k], 8)[0]
+        hm.hm_g1_mul(_p(ark.g1_generator()), _p(kc), _p(out))
+        assert ark.g1_to_py(out)[0] == B.G1.mul(B.G1_GEN, k)
+    out2 = np.zeros(48, dtype=np.uint32)
+    k = rnd.randrange(B.R_MOD)
+    hm.hm_g2_mul(_p(ark.g2_generator()), _p(ark.ints_to_words([k], 8)[0]), _p(out2))
+    assert ark.g2_to_py(out2)[0] == B.G2.mul(B.G2_GEN, k)
+
+
+@pytest.mark.parametrize("c", [3, 8, 11, 13, 15, 16, 17, 20, 23])
+def test_signed_digits_recompose(hm, c):
+    nwin = (256 + c - 1) // c
+    for k in [0, 1, (1 << (c - 1)), (1 << (c - 1)) + 1, B.R_MOD - 1, (1 << 255) - 1] + [rnd.randrange(B.R_MOD) for _ in range(50)]:
+        dig = np.zeros(nwin, dtype=np.int32)
+        hm.hm_signed_digits(_p(ark.ints_to_words([k], 8)[0]), C.c_int(c), C.c_int(nwin), _p(dig))
+        assert all(abs(int(d)) <= 1 << (c - 1) for d in dig)
+        assert sum(int(d) << (c * w) for w, d in enumerate(dig)) == k

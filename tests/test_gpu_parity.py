@@ -1,0 +1,301 @@
+"""GPU parity tests (run on the B200 box): every call goes through the C ABI of libctg_groth16.so
+(contangle-zkcp_b200/ctg) and is compared bit-for-bit with the oracle (oracle/c C++ restatement of
+arkworks 0.3.0, itself pinned against oracle/py and the trapdoor closed form in test_oracle.py)."""
+import random
+
+import numpy as np
+import pytest
+
+import ctg
+from ctg import synthetic as S
+from oracle import ark
+from oracle.py import bls12_381 as B
+from oracle.py import groth16 as G
+from tests import util
+
+pytestmark = pytest.mark.gpu
+rnd = random.Random(424242)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = ctg.Context(0)
+    yield c
+    c.close()
+
+
+def fm(v):
+    return ark.fr_mont_from_ints([v])[0]
+
+
+# ----------------------------------------------------------------------------- fields
+def _edge(mod, n):
+    vals = [0, 1, 2, mod - 1, mod - 2, (1 << 255) % mod, (mod - 1) // 2, 0xFFFFFFFF, 1 << 32, (1 << 64) - 1]
+    return vals + [rnd.randrange(mod) for _ in range(n)]
+
+
+@pytest.mark.parametrize("field,w,mod", [(ctg.FIELD_FR, 8, B.R_MOD), (ctg.FIELD_FQ, 12, B.P_MOD)])
+def test_field_ops(ctx, field, w, mod):
+    av = _edge(mod, 5000)
+    bv = list(reversed(_edge(mod, 5000)))
+    a, b = ark.ints_to_words(av, w), ark.ints_to_words(bv, w)
+    name = "fr" if field == ctg.FIELD_FR else "fq"
+    for op, opn in ((ctg.OP_MUL, "mul"), (ctg.OP_ADD, "add"), (ctg.OP_SUB, "sub")):
+        got = ctx.field_op(field, op, a, b)
+        assert np.array_equal(got, getattr(ark, f"{name}_{opn}")(a, b)), opn
+    assert np.array_equal(ctx.fr_mul(a[:, :8], b[:, :8]) if w == 8 else ctx.fq_mul(a, b), getattr(ark, f"{name}_mul")(a, b))
+
+
+def test_fq2_mul(ctx):
+    n = 3000
+    a = ark.ints_to_words([rnd.randrange(B.P_MOD) for _ in range(2 * n)], 12).reshape(n, 24)
+    b = ark.ints_to_words([rnd.randrange(B.P_MOD) for _ in range(2 * n)], 12).reshape(n, 24)
+    assert np.array_equal(ctx.field_op(ctg.FIELD_FQ2, ctg.OP_MUL, a, b), ark.fq2_mul(a, b))
+
+
+def test_empty_inputs(ctx):
+    e = np.zeros((0, 8), dtype=np.uint32)
+    assert ctx.field_op(ctg.FIELD_FR, ctg.OP_MUL, e, e).shape == (0, 8)
+
+
+# ----------------------------------------------------------------------------- NTT
+@pytest.mark.parametrize("log_n", [0, 1, 2, 3, 7, 10, 11, 12, 13, 16, 19, 20])
+def test_ntt_all_modes(ctx, log_n):
+    x = ark.random_fr_mont(1 << log_n, 1000 + log_n)
+    for inverse, coset in ((False, False), (True, False), (False, True), (True, True)):
+        got = ctx.ntt(x, inverse=inverse, coset=coset)
+        assert np.array_equal(got, ark.ntt_fr(x, inverse=inverse, coset=coset)), (log_n, inverse, coset)
+
+
+@pytest.mark.parametrize("log_n", [22])
+def test_ntt_roundtrip_large(ctx, log_n):
+    # size-independent properties at a BASELINE size: inverse(forward(x)) == x, coset likewise
+    x = ark.random_fr_mont(1 << log_n, 77)
+    assert np.array_equal(ctx.ntt(ctx.ntt(x), inverse=True), x)
+    assert np.array_equal(ctx.ntt(ctx.ntt(x, coset=True), inverse=True, coset=True), x)
+
+
+def test_ntt_rejects_bad_length(ctx):
+    with pytest.raises(ctg.CtgError):
+        ctx.ntt(np.zeros((3, 8), dtype=np.uint32))
+
+
+# ----------------------------------------------------------------------------- bases
+def test_progression_bases_match_oracle(ctx):
+    a, b = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    n = 1000
+    t = ctx.bases_progression_g1(ark.g1_generator(), fm(a), fm(b), n)
+    assert np.array_equal(t.download(), ark.g1_progression(ark.g1_generator(), fm(a), fm(b), n))
+    t.free()
+    t2 = ctx.bases_progression_g2(ark.g2_generator(), fm(a), fm(b), 100)
+    assert np.array_equal(t2.download(), ark.g2_progression(ark.g2_generator(), fm(a), fm(b), 100))
+    t2.free()
+    assert np.array_equal(S.g1_gen_words(), ark.g1_generator()) and np.array_equal(S.g2_gen_words(), ark.g2_generator())
+
+
+def test_precomputed_copies_are_shifted_multiples(ctx):
+    a, b = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    n = 50
+    pts = ark.g1_progression(ark.g1_generator(), fm(a), fm(b), n)
+    pts[3] = 0
+    t = ctx.bases_g1(pts, copies=4, c_bits=8)   # 32 windows -> 8 sets, copy j = 2^(8*8*j) P
+    all_pts = t.download(0, 4 * n).reshape(4, n, 24)
+    assert np.array_equal(all_pts[0], pts)
+    for j in (1, 3):
+        for i in (0, 3, 17):
+            want = ark.g1_mul(pts[i], ark.ints_to_words([1 << (64 * j)], 8)[0])
+            assert np.array_equal(all_pts[j][i], want)
+    t.free()
+
+
+# ----------------------------------------------------------------------------- MSM
+def _g1_bases(n, seed, with_identity=True):
+    r = random.Random(seed)
+    pts = ark.g1_progression(ark.g1_generator(), fm(r.randrange(B.R_MOD)), fm(r.randrange(B.R_MOD)), n)
+    if with_identity and n > 5:
+        pts[5] = 0
+    return pts
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 33, 1000, 1 << 12, (1 << 14) + 7])
+@pytest.mark.parametrize("kind", ["uniform", "poe"])
+def test_msm_g1_vs_oracle(ctx, n, kind):
+    pts = _g1_bases(n, n)
+    sc = ark.random_scalars_canon(n, n + 1, kind)
+    t = ctx.bases_g1(pts)
+    assert np.array_equal(ctx.msm(t, sc), ark.msm_g1(pts, sc))
+    # Montgomery-encoded scalars give the same point
+    assert np.array_equal(ctx.msm(t, ark.fr_to_mont(sc), mont=True), ark.msm_g1(pts, sc))
+    t.free()
+
+
+@pytest.mark.parametrize("kind", ["equal", "rminus1", "zeros", "ones", "duplicates"])
+def test_msm_g1_adversarial(ctx, kind):
+    n = 3000
+    pts = _g1_bases(n, 99)
+    if kind == "zeros":
+        sc = np.zeros((n, 8), dtype=np.uint32)
+    elif kind == "ones":
+        sc = np.zeros((n, 8), dtype=np.uint32); sc[:, 0] = 1
+    elif kind == "duplicates":
+        pts[:] = pts[0]                      # every bucket add hits the doubling path
+        pts[1::2, 12:] = ark.g1_from_py([B.G1.neg(ark.g1_to_py(pts[:1])[0])])[0][12:]   # alternate P, -P
+        sc = ark.random_scalars_canon(n, 5, "equal")
+    else:
+        sc = ark.random_scalars_canon(n, 5, kind)
+    t = ctx.bases_g1(pts)
+    assert np.array_equal(ctx.msm(t, sc), ark.msm_g1(pts, sc)), kind
+    t.free()
+
+
+@pytest.mark.parametrize("c_bits,copies", [(4, 1), (8, 1), (8, 4), (11, 2), (13, 20), (16, 1), (16, 16), (16, 3)])
+def test_msm_g1_window_and_precompute_choices(ctx, c_bits, copies):
+    n = 5000
+    pts = _g1_bases(n, 7)
+    sc = ark.random_scalars_canon(n, 8, "uniform")
+    sc[:50] = ark.random_scalars_canon(50, 9, "rminus1")
+    t = ctx.bases_g1(pts, copies=copies, c_bits=c_bits)
+    assert np.array_equal(ctx.msm(t, sc), ark.msm_g1(pts, sc)), (c_bits, copies)
+    t.free()
+
+
+def test_msm_g1_prefix_and_errors(ctx):
+    n = 2000
+    pts = _g1_bases(n, 3)
+    sc = ark.random_scalars_canon(n, 4)
+    t = ctx.bases_g1(pts)
+    assert np.array_equal(ctx.msm(t, sc[:777]), ark.msm_g1(pts[:777], sc[:777]))   # min(len) semantics
+    assert not ctx.msm(t, sc[:0]).any()                                              # empty -> identity
+    with pytest.raises(ctg.CtgError):
+        ctx.msm(t, np.zeros((n + 1, 8), dtype=np.uint32))
+    t2 = ctx.bases_g2(ark.g2_progression(ark.g2_generator(), fm(1), fm(1), 4))
+    with pytest.raises(ctg.CtgError):
+        load_fn = ctg.load().ctg_msm_g1
+        ctx._check(load_fn(ctx.h, t2.handle, None, 0, 0, None))
+    t.free(); t2.free()
+
+
+@pytest.mark.parametrize("n,kind", [(1, "uniform"), (40, "poe"), (1500, "uniform"), (4096, "poe")])
+def test_msm_g2_vs_oracle(ctx, n, kind):
+    pts = ark.g2_progression(ark.g2_generator(), fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD)), n)
+    if n > 5:
+        pts[2] = 0
+    sc = ark.random_scalars_canon(n, n + 11, kind)
+    t = ctx.bases_g2(pts)
+    assert np.array_equal(ctx.msm(t, sc), ark.msm_g2(pts, sc))
+    t.free()
+    t = ctx.bases_g2(pts, copies=3, c_bits=9)
+    assert np.array_equal(ctx.msm(t, sc), ark.msm_g2(pts, sc))
+    t.free()
+
+
+@pytest.mark.parametrize("log_n,kind", [(16, "uniform"), (18, "poe"), (20, "uniform")])
+def test_msm_g1_dlog_closed_form_large(ctx, log_n, kind):
+    """Bases generated on the device with known discrete logs: the MSM must equal (sum s_i (a + i b)) G."""
+    n = 1 << log_n
+    a, b = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    t = ctx.bases_progression_g1(ark.g1_generator(), fm(a), fm(b), n, copies=2)
+    sc = ark.random_scalars_canon(n, log_n, kind)
+    got = ark.g1_to_py(ctx.msm(t, sc))[0]
+    s_int = ark.words_to_ints(sc)
+    dl = (a * sum(s_int) + b * sum(i * s for i, s in enumerate(s_int))) % B.R_MOD
+    assert got == B.G1.mul(B.G1_GEN, dl)
+    t.free()
+
+
+def test_msm_partials_combine(ctx):
+    """Point-range sharding as the multi-GPU path does it: partial sums per range, combined on one device."""
+    n = 6000
+    pts = _g1_bases(n, 21)
+    sc = ark.random_scalars_canon(n, 22)
+    parts = []
+    for lo, hi in ((0, 1500), (1500, 3000), (3000, 4500), (4500, 6000)):
+        t = ctx.bases_g1(pts[lo:hi])
+        parts.append(ctx.msm_partial(t, sc[lo:hi]))
+        t.free()
+    assert np.array_equal(ctx.combine(np.stack(parts), group=1), ark.msm_g1(pts, sc))
+
+
+# ----------------------------------------------------------------------------- witness map and prover
+def _trapdoor():
+    return G.Trapdoor(*[rnd.randrange(1, B.R_MOD) for _ in range(5)],
+                      B.G1.mul(B.G1_GEN, rnd.randrange(1, B.R_MOD)), B.G2.mul(B.G2_GEN, rnd.randrange(1, B.R_MOD)))
+
+
+@pytest.mark.parametrize("log_n", [2, 3, 6, 10, 12, 14])
+def test_witness_map_vs_oracle(ctx, log_n):
+    r1cs, zm, z = S.mul_chain(log_n)
+    d = ctx.upload_r1cs(r1cs)
+    assert np.array_equal(ctx.witness_map(d, zm), ark.witness_map(r1cs, zm))
+    d.free()
+
+
+def test_witness_map_poe_shape(ctx):
+    r1cs, zm, z = S.poe_shape(100)
+    d = ctx.upload_r1cs(r1cs)
+    h = ctx.witness_map(d, zm)
+    assert np.array_equal(h, ark.witness_map(r1cs, zm))
+    assert not h[-1].any()     # deg h <= n - 2
+    d.free()
+
+
+@pytest.mark.parametrize("log_n,r_zero,copies", [(3, False, 1), (5, True, 1), (8, False, 1), (10, False, 4)])
+def test_prove_trapdoor_key_vs_oracle_and_closed_form(ctx, log_n, r_zero, copies):
+    cs, z = G.mul_chain(log_n, rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD))
+    td = _trapdoor()
+    pk = util.trapdoor_pk_arrays(cs, td)
+    r1 = ark.r1cs_from_py(cs)
+    r = 0 if r_zero else rnd.randrange(B.R_MOD)
+    s = rnd.randrange(B.R_MOD)
+    zm = ark.fr_mont_from_ints(z)
+    dpk = ctx.upload_pk(pk, cs.num_instance, cs.num_constraints, copies=copies)
+    dr = ctx.upload_r1cs(r1)
+    got = ctx.prove(dpk, dr, zm, fm(r), fm(s))
+    want = ark.create_proof(pk, r1, zm, fm(r), fm(s))
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    if not r_zero:
+        assert util.proof_to_py(got) == G.closed_form_proof(cs, td, z, r, s)
+    dpk.free(); dr.free()
+
+
+def test_prove_poe_shape_vs_oracle(ctx):
+    r1cs, zm, z = S.poe_shape(100)
+    pk, dl = S.progression_pk(ctx, r1cs)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"])
+    dr = ctx.upload_r1cs(r1cs)
+    got, tm = ctx.prove(dpk, dr, zm, fm(r), fm(s), timed=True)
+    want = ark.create_proof(pk, r1cs, zm, fm(r), fm(s))
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    assert tm["total_ms"] > 0
+    dpk.free(); dr.free()
+
+
+@pytest.mark.parametrize("log_n", [16])
+def test_prove_progression_key_dlog_closed_form(ctx, log_n):
+    """Full-size pin that needs no MSM / NTT oracle for the group part: the key's discrete logs are known."""
+    r1cs, zm, z = S.mul_chain(log_n)
+    pk, dl = S.progression_pk(ctx, r1cs)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], copies=2)
+    dr = ctx.upload_r1cs(r1cs)
+    got = ctx.prove(dpk, dr, zm, fm(r), fm(s))
+    h = ark.fr_ints_from_mont(ark.witness_map(r1cs, zm))
+    assert util.proof_to_py(got) == util.dlog_expected_proof(dl, r1cs, z, h, r, s)
+    dpk.free(); dr.free()
+
+
+def test_prove_rejects_mismatched_shapes(ctx):
+    r1a, zma, _ = S.mul_chain(4)
+    r1b, zmb, _ = S.mul_chain(5)
+    pk, _ = S.progression_pk(ctx, r1a)
+    dpk = ctx.upload_pk(pk, r1a["num_instance"], r1a["num_constraints"])
+    drb = ctx.upload_r1cs(r1b)
+    with pytest.raises(ctg.CtgError):
+        ctx.prove(dpk, drb, zmb, fm(1), fm(2))
+    bad = dict(pk); bad["h_query"] = pk["h_query"][:-1]
+    with pytest.raises(ctg.CtgError):
+        ctx.upload_pk(bad, r1a["num_instance"], r1a["num_constraints"])
+    dpk.free(); drb.free()

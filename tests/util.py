@@ -1,0 +1,60 @@
+"""Test helpers: trapdoor keys built with the C++ oracle's fixed-base multiplier, and the
+discrete-log closed form for progression keys (ctg.synthetic.progression_pk)."""
+import numpy as np
+
+from oracle import ark
+from oracle.py import bls12_381 as B
+from oracle.py import groth16 as G
+
+
+def trapdoor_pk_arrays(cs, td):
+    """ark-groth16 generate_parameters (oracle/py/groth16.py) with the scalar multiplications done by
+    oracle/c (fast enough for 2^12-2^14 domains).  cs: oracle.py R1CS; td: Trapdoor (ints, affine gens)."""
+    n = cs.domain_size
+    log_n = n.bit_length() - 1
+    u = ark.fr_ints_from_mont(ark.lagrange_coeffs(log_n, ark.fr_mont_from_ints([td.tau])[0]))
+    m, ni = cs.num_vars, cs.num_instance
+    a, b, c = [0] * m, [0] * m, [0] * m
+    for i in range(cs.num_constraints):
+        for cf, j in cs.a[i]:
+            a[j] = (a[j] + u[i] * cf) % B.R_MOD
+        for cf, j in cs.b[i]:
+            b[j] = (b[j] + u[i] * cf) % B.R_MOD
+        for cf, j in cs.c[i]:
+            c[j] = (c[j] + u[i] * cf) % B.R_MOD
+    for j in range(ni):
+        a[j] = (a[j] + u[cs.num_constraints + j]) % B.R_MOD
+    zt = (pow(td.tau, n, B.R_MOD) - 1) % B.R_MOD
+    dinv = B.fr_inv(td.delta)
+    g1, g2 = ark.g1_from_py([td.g1])[0], ark.g2_from_py([td.g2])[0]
+    fb1 = lambda ks: ark.g1_fixed_base(g1, ark.fr_mont_from_ints([k % B.R_MOD for k in ks]))
+    fb2 = lambda ks: ark.g2_fixed_base(g2, ark.fr_mont_from_ints([k % B.R_MOD for k in ks]))
+    abc = [(td.beta * a[i] + td.alpha * b[i] + c[i]) % B.R_MOD for i in range(m)]
+    hs, t = [], zt * dinv % B.R_MOD
+    for _ in range(n - 1):
+        hs.append(t)
+        t = t * td.tau % B.R_MOD
+    singles = fb1([td.alpha, td.beta, td.delta])
+    singles2 = fb2([td.beta, td.delta])
+    return {"alpha_g1": singles[0], "beta_g1": singles[1], "delta_g1": singles[2], "beta_g2": singles2[0], "delta_g2": singles2[1],
+            "a_query": fb1(a), "b_g1_query": fb1(b), "b_g2_query": fb2(b), "h_query": fb1(hs),
+            "l_query": fb1([abc[i] * dinv for i in range(ni, m)]) if m > ni else np.zeros((0, 24), dtype=np.uint32)}
+
+
+def dlog_expected_proof(dl, r1cs, z, h, r, s):
+    """Expected (A, B, C) for a progression key (dl from ctg.synthetic.progression_pk): every base has a
+    known discrete log, so each proof element is ONE scalar multiplication of the generator.
+    z, h: ints (h natural order, n entries); r, s ints."""
+    R = B.R_MOD
+    ni = r1cs["num_instance"]
+    m = len(z)
+    lin = lambda key, vals: sum(v * (dl[key][0] + i * dl[key][1]) for i, v in enumerate(vals)) % R
+    ea = (dl["alpha"] + r * dl["delta"] + lin("a", z)) % R
+    eb = (dl["beta"] + s * dl["delta"] + lin("b", z)) % R
+    ec = (s * ea + r * eb - r * s % R * dl["delta"] + lin("l", z[ni:]) + lin("h", h[:len(h) - 1])) % R
+    return B.G1.mul(B.G1_GEN, ea), B.G2.mul(B.G2_GEN, eb), B.G1.mul(B.G1_GEN, ec)
+
+
+def proof_to_py(proof):
+    a, b, c = proof
+    return ark.g1_to_py(a)[0], ark.g2_to_py(b)[0], ark.g1_to_py(c)[0]
