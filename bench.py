@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's measurement contract for the Groth16 prover hot path.
+
+Headline workload (BASELINE.json configs[1]): one "step" = one G1 variable-base MSM over 2^22
+uniformly random BLS12-381 scalars and 2^22 distinct subgroup bases (generated on the device),
+through the C ABI of libctg_groth16.so.  N > 1 (torchrun, one rank per GPU): the MSM is sharded by
+point range -- every rank owns 2^22 points (weak scaling), computes the projective partial sum on
+its GPU, the 192-byte partials are all-gathered with NCCL and rank 0 combines them.
+
+  value  : points/s with scalars already resident in HBM (device pointers in, projective sum out)
+  e2e    : points/s through the host-buffer entry point (pinned scalars H2D + affine result D2H inside)
+  roofline : bucket-accumulation kernel (the dominant launch) against the MEASURED integer-pipe peak
+  cpu_baseline : the arkworks-0.3.0 algorithm restatement (oracle/c) on the host cores, bounded sample
+  --impl reference : times that same CPU restatement as the reference arm
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "contangle-zkcp_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+MAC32_PER_G1_POINT = 48_000      # 16 signed windows x (8M + 2S) x 300 MAC32 per Fq product
+METRIC = "g1_msm_throughput"
+UNIT = "Mpts/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--log-n", type=int, default=22)
+    ap.add_argument("--copies", type=int, default=int(os.environ.get("CTG_BENCH_COPIES", "0")), help="precomputed multiples per base (0 = library default)")
+    ap.add_argument("--c-bits", type=int, default=0)
+    ap.add_argument("--cpu-sample-log-n", type=int, default=20)
+    ap.add_argument("--no-extras", action="store_true", help="skip the NTT / prove / size-sweep extras")
+    return ap.parse_args()
+
+
+def workload_name(log_n, n_gpus):
+    return f"G1 MSM, 2^{log_n} uniform scalars x distinct subgroup bases per GPU" + (f", point-range sharded over {n_gpus} GPUs" if n_gpus > 1 else "")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._halt = index, [], threading.Event()
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def finish(self):
+        self._halt.set()
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_msm_sample(bases_host, scalars_host, steps=1):
+    """Time the arkworks-algorithm C++ restatement (oracle/c) on all host threads.  Baseline leg only."""
+    from oracle import ark
+    ark.lib()
+    best = None
+    out = None
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        out = ark.msm_g1(bases_host, scalars_host)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return best, out, ark.threads()
+
+
+def reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path = arkworks' VariableBaseMSM.  arkworks cannot
+    be built here (no Rust), so the arm times the C++ restatement of its algorithm (oracle/c) with all
+    the host threads that algorithm can use (one task per window, as rayon does), on a bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ark
+    from ctg import synthetic as S
+    n = 1 << min(args.cpu_sample_log_n, args.log_n)
+    t0 = time.perf_counter()
+    a, b = S.fr_mont([0xC0FFEE + args.log_n])[0], S.fr_mont([0x5EED])[0]
+    bases = ark.g1_progression(ark.g1_generator(), a, b, n)
+    scalars = ark.random_scalars_canon(n, 0xC0FFEE + args.log_n, "uniform")
+    gen_s = time.perf_counter() - t0
+    for _ in range(min(args.warmup, 1)):
+        ark.msm_g1(bases, scalars)
+    times = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        ark.msm_g1(bases, scalars)
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    val = n / (ms * 1e-3) / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 limbs (381-bit Fq, 255-bit Fr)", "data": "synthetic",
+            "config": {"workload": workload_name(args.log_n, args.gpus), "sample": f"2^{n.bit_length() - 1} points of the same workload per step"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": ark.threads(), "kind": "port",
+                             "sample": f"arkworks-0.3.0 VariableBaseMSM algorithm restated in C++ (oracle/c), 2^{n.bit_length() - 1} points, input generation {gen_s:.1f}s untimed"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    import torch
+    import ctg
+    from ctg import synthetic as S
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    stream = torch.cuda.current_stream()
+    ctx = ctg.Context(local, stream=stream.cuda_stream)
+
+    n = 1 << args.log_n
+    seed = 0xC0FFEE + args.log_n
+    # bases: P_i = (a + (rank*n + i) b) G, generated on the device; scalars: uniform < 2^254 (valid canonical Fr)
+    a_int, b_int = seed, 0x5EED
+    a_rank = (a_int + rank * n * b_int) % S.R_MOD
+    bases = ctx.bases_progression_g1(S.g1_gen_words(), S.fr_mont([a_rank])[0], S.fr_mont([b_int])[0], n, copies=args.copies, c_bits=args.c_bits)
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed + rank)
+    d_scalars = torch.randint(0, 1 << 32, (n, 8), generator=g, device=dev, dtype=torch.int64).to(torch.int32)
+    d_scalars[:, 7] &= 0x3FFFFFFF
+    h_scalars = torch.empty((n, 8), dtype=torch.int32, pin_memory=True)
+    h_scalars.copy_(d_scalars)
+    d_part = torch.zeros(48, dtype=torch.int32, device=dev)            # one G1 XYZZ partial
+    d_all = torch.zeros((world, 48), dtype=torch.int32, device=dev)
+    d_aff = torch.zeros(24, dtype=torch.int32, device=dev)
+    h_np = h_scalars.numpy().view(np.uint32)
+
+    def step_device():
+        ctx.msm_dev(bases, d_scalars.data_ptr(), n, d_part.data_ptr())
+        if world > 1:
+            dist.all_gather_into_tensor(d_all, d_part)
+            if rank == 0:
+                ctx.combine_dev(d_all.data_ptr(), world, d_aff.data_ptr())
+
+    def step_e2e():
+        if world == 1:
+            return ctx.msm(bases, h_np)                       # H2D scalars + MSM + to_affine + D2H inside
+        part = ctx.msm_partial(bases, h_np)                   # H2D + MSM + D2H of the 192-byte partial
+        d_part.copy_(torch.from_numpy(part.view(np.int32)))
+        dist.all_gather_into_tensor(d_all, d_part)
+        if rank == 0:
+            return ctx.combine(d_all.cpu().numpy().view(np.uint32), group=1)
+        return None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms = e0.elapsed_time(e1)
+        t = torch.tensor([ms, wall], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]) / steps, float(t[1]) / steps
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches0 = ctx.launches
+    ms_dev, _ = timed(step_device, args.steps)
+    launches = ctx.launches - launches0
+    for _ in range(2):
+        step_e2e()
+    ms_e2e_dev, ms_e2e_wall = timed(step_e2e, args.steps)
+    ms_e2e = max(ms_e2e_dev, ms_e2e_wall)   # host-blocking API: the wall clock around it is the honest figure
+    # dominant kernel, live: CUDA events inside the library around the accumulate launch (on the same stream)
+    acc_ms, sort_ms, red_ms = [], [], []
+    for _ in range(args.steps):
+        ctx.msm_dev(bases, d_scalars.data_ptr(), n, d_part.data_ptr(), timed=True)
+        t = ctx.last_timings()
+        acc_ms.append(t["msm_accumulate_ms"]); sort_ms.append(t["msm_sort_ms"]); red_ms.append(t["msm_reduce_ms"])
+    clocks = sampler.finish() if sampler else None
+    acc = sum(acc_ms) / len(acc_ms)
+    imad_per_s, fq_mul_per_s = ctx.imad_peak_probe()
+    mac_peak = imad_per_s / 2.0          # a 32x32->64 MAC costs two IMAD issue slots (profiles/r01_pipe_probe.txt)
+    achieved = n * MAC32_PER_G1_POINT / (acc * 1e-3)
+
+    line = {
+        "metric": METRIC, "value": world * n / (ms_dev * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32 limbs (381-bit Fq, 255-bit Fr)", "data": "synthetic",
+        "config": {"workload": workload_name(args.log_n, world), "points_per_gpu": n, "l2": "inputs (128 MiB scalars + 384 MiB bases per copy) exceed the 126 MB L2",
+                   "window_bits": None, "precomputed_copies": args.copies, "seed": seed},
+        "e2e": {"value": world * n / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": 96 if world == 1 else 192,
+                "ms_per_step": ms_e2e, "ms_per_step_device_events": ms_e2e_dev},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "imad", "kernel": "msm_accumulate_kernel<Fq>", "achieved": achieved / 1e12, "peak": mac_peak / 1e12, "unit": "TMAC32/s",
+                     "frac": achieved / mac_peak, "traffic": None, "kernel_ms": acc, "step_share": acc / ms_dev,
+                     "peak_source": "measured live: ctg_imad_peak_probe IMAD issue rate / 2 (32x32->64 MAC = 2 IMAD slots)",
+                     "imad_per_s": imad_per_s, "fq_mul_per_s": fq_mul_per_s, "algorithmic_mac32_per_point": MAC32_PER_G1_POINT},
+        "stages_ms": {"sort": sum(sort_ms) / len(sort_ms), "accumulate": acc, "reduce": sum(red_ms) / len(red_ms)},
+    }
+
+    if rank == 0 and world == 1:
+        # CPU baseline on a bounded sample of the same workload; doubles as a live parity check
+        ns = 1 << min(args.cpu_sample_log_n, args.log_n)
+        hb = bases.download(0, ns)
+        hs = np.ascontiguousarray(h_np[:ns])
+        secs, cpu_pt, cores = cpu_msm_sample(hb, hs)
+        gpu_pt = ctx.msm(bases, hs)
+        line["cpu_baseline"] = {"value": ns / secs / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"first 2^{ns.bit_length() - 1} points of the workload, arkworks-0.3.0 algorithm restated in C++ (oracle/c), {secs:.2f}s",
+                                "gpu_matches_cpu_on_sample": bool(np.array_equal(cpu_pt, gpu_pt))}
+        if not args.no_extras:
+            line["extra"] = extras(ctx, torch, dev, stream, S, args)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    bases.free()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def extras(ctx, torch, dev, stream, S, args):
+    """Other rows of the metric (reported, not the headline): NTT GB/s, MSM size sweep, Groth16 prove ms."""
+    out = {}
+
+    def ev_time(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    hbm = None
+    try:
+        hbm = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        pass
+    ntt = {}
+    for lg in (16, 20, 22, 24):
+        x = torch.randint(0, 1 << 30, (1 << lg, 8), device=dev, dtype=torch.int32)
+        ms = ev_time(lambda: ctx.ntt_dev(x.data_ptr(), lg), 5)
+        gbs = 64.0 * (1 << lg) / (ms * 1e-3) / 1e9
+        ntt[f"2^{lg}"] = {"ms": ms, "algorithmic_GBps": gbs, "frac_of_hbm_peak": (gbs / hbm) if hbm else None}
+        del x
+    out["ntt_fr_forward_natural_to_natural"] = ntt
+    msm = {}
+    for lg in (16, 18, 20):
+        n = 1 << lg
+        b = ctx.bases_progression_g1(S.g1_gen_words(), S.fr_mont([77 + lg])[0], S.fr_mont([3])[0], n, copies=args.copies)
+        sc = torch.randint(0, 1 << 30, (n, 8), device=dev, dtype=torch.int32)
+        res = torch.zeros(48, dtype=torch.int32, device=dev)
+        ms = ev_time(lambda: ctx.msm_dev(b, sc.data_ptr(), n, res.data_ptr()), 5)
+        msm[f"2^{lg}"] = {"ms": ms, "Mpts_per_s": n / (ms * 1e-3) / 1e6}
+        b.free()
+    out["g1_msm_device_resident"] = msm
+    # Groth16 prove (config 3 shape, MulChain) with device-resident key and R1CS
+    for lg in (16, 20):
+        r1cs, zm, _ = S.mul_chain(lg)
+        pk, _ = S.progression_pk(ctx, r1cs)
+        dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], copies=args.copies)
+        dr = ctx.upload_r1cs(r1cs)
+        del pk
+        r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
+        for _ in range(2):
+            ctx.prove(dpk, dr, zm, r, s)
+        ts = []
+        for _ in range(5):
+            t0 = time.perf_counter()
+            _, tm = ctx.prove(dpk, dr, zm, r, s, timed=True)
+            ts.append(((time.perf_counter() - t0) * 1e3, tm))
+        ts.sort(key=lambda x: x[0])
+        wall, tm = ts[len(ts) // 2]
+        out[f"groth16_prove_mulchain_2^{lg}"] = {"wall_ms_median": wall, "stages_ms": tm}
+        dpk.free(); dr.free()
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -221,7 +221,7 @@ static int32_t bases_new(ctg_ctx* ctx, int group, uint64_t n, int copies, int c_
   ctg_bases* h = new ctg_bases();
   h->b.group = group;
   h->b.n = n;
-  h->b.plan = msm_make_plan(n, copies, c_bits);
+  h->b.plan = msm_make_plan(n, copies, c_bits, group == 1 ? sizeof(G1Affine) : sizeof(G2Affine));
   if (n * (uint64_t)h->b.plan.copies >= (1ull << 31)) { delete h; return fail(ctx, CTG_ERR_INVALID, "bases: n * copies must be < 2^31"); }
   const size_t eb = group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
   const size_t bytes = (size_t)h->b.plan.copies * (n ? n : 1) * eb;

@@ -35,6 +35,7 @@ struct MsmWorkspace {
   uint32_t* part_gb = nullptr;  // [2 * T]
   void* chunk = nullptr;        // bucket-reduction partials
   void* result = nullptr;       // 1 XYZZ
+  uint32_t* tile_sums = nullptr;  // scan scratch
   size_t cap_nb = 0, cap_entries = 0, cap_bucket_bytes = 0, cap_part_bytes = 0, cap_chunk_bytes = 0;
   int part_threads = 0;
 };
@@ -111,7 +112,7 @@ int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_
 int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);        // natural in, bit-reversed out
 
 // msm_g1.cu / msm_g2.cu
-MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override);
+MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes);
 int32_t msm_g1_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,
                    G1XYZZ* d_out, cudaStream_t st, float* stage_ms);
 int32_t msm_g2_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,

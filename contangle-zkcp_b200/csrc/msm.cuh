@@ -76,35 +76,66 @@ template <class F> __global__ void msm_count_kernel(const uint32_t* __restrict__
   }
 }
 
-// ---- 2. exclusive scan (one CTA; nb <= 2^20) ------------------------------------------------
-template <class F> __global__ void __launch_bounds__(1024) msm_scan_kernel(uint32_t* counts, uint32_t* cursor, uint32_t nb) {
-  __shared__ uint32_t sums[1024];
-  const uint32_t tid = threadIdx.x;
-  const uint32_t per = (nb + 1023) / 1024;
-  const uint32_t lo = min(nb, tid * per), hi = min(nb, lo + per);
+// ---- 2. exclusive scan of the bucket sizes: per-tile sums, scan of the tile sums, per-tile scan ----
+static constexpr int kScanTile = 2048;  // entries per CTA (256 threads x 8)
+template <class F> __global__ void __launch_bounds__(256) msm_scan_tile_sum_kernel(const uint32_t* __restrict__ counts, uint32_t nb, uint32_t* tile_sums) {
+  __shared__ uint32_t sh[256];
+  const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * 8;
   uint32_t s = 0;
-  for (uint32_t i = lo; i < hi; i++) s += counts[i];
-  sums[tid] = s;
+#pragma unroll
+  for (int k = 0; k < 8; k++) if (base + k < nb) s += counts[base + k];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int off = 128; off >= 1; off >>= 1) {
+    if ((int)threadIdx.x < off) sh[threadIdx.x] += sh[threadIdx.x + off];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = sh[0];
+}
+// one CTA: exclusive scan of up to 1024 tile sums in place; tile_sums[ntiles] = grand total
+template <class F> __global__ void __launch_bounds__(1024) msm_scan_tiles_kernel(uint32_t* tile_sums, uint32_t ntiles) {
+  __shared__ uint32_t sh[1024];
+  const uint32_t tid = threadIdx.x;
+  const uint32_t v = tid < ntiles ? tile_sums[tid] : 0;
+  sh[tid] = v;
   __syncthreads();
   for (uint32_t off = 1; off < 1024; off <<= 1) {
-    uint32_t v = tid >= off ? sums[tid - off] : 0;
+    uint32_t x = tid >= off ? sh[tid - off] : 0;
     __syncthreads();
-    sums[tid] += v;
+    sh[tid] += x;
     __syncthreads();
   }
-  uint32_t run = sums[tid] - s;
-  for (uint32_t i = lo; i < hi; i++) {
-    uint32_t c = counts[i];
-    counts[i] = run;
-    cursor[i] = run;
-    run += c;
+  if (tid < ntiles) tile_sums[tid] = sh[tid] - v;
+  if (tid == 1023) tile_sums[ntiles] = sh[1023];
+}
+template <class F> __global__ void __launch_bounds__(256) msm_scan_apply_kernel(uint32_t* counts, uint32_t* cursor, uint32_t nb, const uint32_t* __restrict__ tile_sums,
+                                                                               uint32_t ntiles) {
+  __shared__ uint32_t sh[256];
+  const uint32_t tid = threadIdx.x;
+  const uint32_t base = blockIdx.x * kScanTile + tid * 8;
+  uint32_t c[8], s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) { c[k] = base + k < nb ? counts[base + k] : 0; s += c[k]; }
+  sh[tid] = s;
+  __syncthreads();
+  for (uint32_t off = 1; off < 256; off <<= 1) {
+    uint32_t x = tid >= off ? sh[tid - off] : 0;
+    __syncthreads();
+    sh[tid] += x;
+    __syncthreads();
   }
-  if (tid == 1023) counts[nb] = sums[1023];
+  uint32_t run = tile_sums[blockIdx.x] + sh[tid] - s;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    if (base + k < nb) { counts[base + k] = run; cursor[base + k] = run; }
+    run += c[k];
+  }
+  if (blockIdx.x == 0 && tid == 0) counts[nb] = tile_sums[ntiles];
 }
 
 // ---- 3. scatter ---------------------------------------------------------------------------
-template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, uint64_t n, int mont, MsmPlan plan, uint32_t* cursor,
-                                                      uint32_t* entries) {
+template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t copy_stride, int mont, MsmPlan plan,
+                                                      uint32_t* cursor, uint32_t* entries) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const uint64_t n32 = (n + 31) & ~31ull;
   const unsigned lane = threadIdx.x & 31;
@@ -131,7 +162,7 @@ template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict
       base = __shfl_sync(0xffffffffu, base, leader);
       if (key != kNoBucket) {
         uint32_t copy = (uint32_t)(w / plan.nsets);
-        entries[base + __popc(peers & lt_mask)] = (uint32_t)(copy * n + i) | (d < 0 ? 0x80000000u : 0u);
+        entries[base + __popc(peers & lt_mask)] = (uint32_t)(copy * copy_stride + i) | (d < 0 ? 0x80000000u : 0u);
       }
     }
   }
@@ -159,6 +190,35 @@ template <class F> __device__ __forceinline__ XYZZ<F> warp_sum(XYZZ<F> acc, XYZZ
   return acc;
 }
 
+// 5a. one thread per run head: runs that end within kShortRun slots (the common case: a bucket cut once) are summed
+//     sequentially; longer runs (huge buckets of skewed scalar distributions) get kLongBit for the warp kernel below.
+static constexpr uint32_t kLongBit = 0x40000000u;
+static constexpr uint32_t kTagMask = 0x3fffffffu;
+static constexpr uint32_t kShortRun = 8;
+template <class F> __global__ void __launch_bounds__(128) msm_fixup_short_kernel(const XYZZ<F>* part_pt, uint32_t* part_gb, uint32_t nslots, XYZZ<F>* buckets) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  const uint32_t tag = part_gb[s];
+  if (tag == kNoBucket || !(tag & kHeadBit)) return;
+  const uint32_t gb = tag & kTagMask;
+  XYZZ<F> acc;
+  copy16(acc, part_pt[s]);
+  uint32_t j = s + 1;
+  const uint32_t lim = (s + 1 + kShortRun < nslots) ? s + 1 + kShortRun : nslots;
+  bool ended = false;
+  for (; j < lim; j++) {
+    const uint32_t g = part_gb[j];
+    if (g == kNoBucket) continue;
+    if ((g & kTagMask) != gb) { ended = true; break; }
+    XYZZ<F> o;
+    copy16(o, part_pt[j]);
+    acc = xyzz_add(acc, o);
+  }
+  if (ended || j >= nslots) copy16(buckets[gb], acc);
+  else part_gb[s] = tag | kLongBit;
+}
+
+// 5b. long runs: one warp per run, lanes stride over the partials, then a shared-memory tree
 template <class F> __global__ void __launch_bounds__(64) msm_fixup_kernel(const XYZZ<F>* part_pt, const uint32_t* __restrict__ part_gb, uint32_t nslots,
                                                                          XYZZ<F>* buckets) {
   __shared__ XYZZ<F> sh[2][32];
@@ -167,22 +227,22 @@ template <class F> __global__ void __launch_bounds__(64) msm_fixup_kernel(const 
   if (slot0 >= nslots) return;
   const uint32_t my = slot0 + lane;
   const uint32_t tag = my < nslots ? part_gb[my] : kNoBucket;
-  unsigned heads = __ballot_sync(0xffffffffu, tag != kNoBucket && (tag & kHeadBit));
+  unsigned heads = __ballot_sync(0xffffffffu, tag != kNoBucket && (tag & kLongBit));
   while (heads) {
     const int h = __ffs(heads) - 1;
     heads &= heads - 1;
-    const uint32_t gb = __shfl_sync(0xffffffffu, tag, h) & ~kHeadBit;
+    const uint32_t gb = __shfl_sync(0xffffffffu, tag, h) & kTagMask;
     XYZZ<F> acc = XYZZ<F>::inf();
     for (uint32_t base = slot0 + h;; base += 32) {
       const uint32_t s = base + lane;
       const uint32_t g = s < nslots ? part_gb[s] : kNoBucket;
-      const bool mine = g != kNoBucket && (g & ~kHeadBit) == gb;
+      const bool mine = g != kNoBucket && (g & kTagMask) == gb;
       if (mine) {
         XYZZ<F> o;
         copy16(o, part_pt[s]);
         acc = xyzz_add(acc, o);
       }
-      const bool stop = s >= nslots || (g != kNoBucket && (g & ~kHeadBit) != gb);
+      const bool stop = s >= nslots || (g != kNoBucket && (g & kTagMask) != gb);
       if (__any_sync(0xffffffffu, stop)) break;
     }
     acc = warp_sum(acc, sh[wib], lane);
@@ -410,6 +470,7 @@ template <class F> struct MsmHost {
       ws.cap_chunk_bytes = cb;
     }
     if (!ws.result) CTG_CUDA(ctx, cudaMalloc(&ws.result, sizeof(XYZZ<Fq2>)));
+    if (!ws.tile_sums) CTG_CUDA(ctx, cudaMalloc(&ws.tile_sums, 1025 * sizeof(uint32_t)));
     return CTG_OK;
   }
 
@@ -447,9 +508,15 @@ template <class F> struct MsmHost {
     const int dig_blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx->sm_count * 8);
     msm_count_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, mont ? 1 : 0, plan, ws.counts);
     CTG_KERNEL_CHECK(ctx);
-    msm_scan_kernel<F><<<1, 1024, 0, st>>>(ws.counts, ws.cursor, nb);
+    const uint32_t ntiles = (nb + kScanTile - 1) / kScanTile;
+    if (ntiles > 1023) return fail(ctx, CTG_ERR_INVALID, "msm: too many buckets for the scan (c too large)");
+    msm_scan_tile_sum_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, nb, ws.tile_sums);
     CTG_KERNEL_CHECK(ctx);
-    msm_scatter_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, mont ? 1 : 0, plan, ws.cursor, ws.entries);
+    msm_scan_tiles_kernel<F><<<1, 1024, 0, st>>>(ws.tile_sums, ntiles);
+    CTG_KERNEL_CHECK(ctx);
+    msm_scan_apply_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, ws.cursor, nb, ws.tile_sums, ntiles);
+    CTG_KERNEL_CHECK(ctx);
+    msm_scatter_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, bases.n, mont ? 1 : 0, plan, ws.cursor, ws.entries);
     CTG_KERNEL_CHECK(ctx);
     if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
 
@@ -459,6 +526,8 @@ template <class F> struct MsmHost {
     if (blocks < 1) blocks = 1;
     const uint32_t nslots = (uint32_t)blocks * 128 * 2;
     accumulate_launch<F>(blocks, st, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, ws.counts, nb, buckets, part_pt, ws.part_gb);
+    CTG_KERNEL_CHECK(ctx);
+    msm_fixup_short_kernel<F><<<(nslots + 127) / 128, 128, 0, st>>>(part_pt, ws.part_gb, nslots, buckets);
     CTG_KERNEL_CHECK(ctx);
     msm_fixup_kernel<F><<<(nslots / 32 + 1) / 2, 64, 0, st>>>(part_pt, ws.part_gb, nslots, buckets);
     CTG_KERNEL_CHECK(ctx);

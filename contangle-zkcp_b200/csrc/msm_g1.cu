@@ -5,22 +5,30 @@
 
 namespace ctg {
 
-// Window size: minimise  windows * n  (mixed additions)  +  3.5 * sets * 2^(c-1)  (bucket reduction,
-// two full additions per bucket plus the chunk offsets).  Windows are signed, so c bits need
-// 2^(c-1) buckets; c <= 16 keeps a bucket set at 2^15 entries.
-MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override) {
+// Plan selection.  Cost model in microseconds, constants measured on B200 (profiles/r01_*):
+//   bucket accumulation   windows * n mixed additions at ~2.5 G/s,
+//   bucket reduction      ~6 ns per bucket (two full additions + chunk offsets, latency-bound),
+//   window combine        c * (sets - 1) sequential doublings at ~11 us each (one thread),
+// Windows are signed, so c bits need 2^(c-1) buckets; c <= 16 keeps a bucket set at 2^15 entries.
+// copies_wanted = 0: keep as many precomputed multiples 2^(c G j) P as fit a 12 GiB table.
+MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes) {
   MsmPlan best{};
   double best_cost = -1;
+  const double budget = 12.0 * 1024 * 1024 * 1024;
+  const uint64_t nn = n ? n : 1;
   for (int c = 2; c <= 16; c++) {
     if (c_override > 0 && c != c_override) continue;
     MsmPlan p;
     p.c = c;
     p.nwin = msm_num_windows(c);
-    p.copies = copies_wanted <= 0 ? 1 : std::min(copies_wanted, p.nwin);
+    int cap = (int)std::min<double>(p.nwin, std::max(1.0, budget / ((double)nn * (double)point_bytes)));
+    if (cap > 32) cap = 32;  // precompute_kernel keeps at most 32 multiples per base
+    while ((uint64_t)cap * nn >= (1ull << 31) && cap > 1) cap--;
+    p.copies = copies_wanted <= 0 ? cap : std::min(copies_wanted, p.nwin);
     p.nsets = (p.nwin + p.copies - 1) / p.copies;
     p.copies = (p.nwin + p.nsets - 1) / p.nsets;  // drop copies no window would use
     p.nbuckets_per_set = 1u << (c - 1);
-    double cost = (double)p.nwin * (double)(n ? n : 1) + 3.5 * p.nsets * (double)p.nbuckets_per_set + 40.0 * c * (p.nsets - 1);
+    double cost = 0.0004 * p.nwin * (double)nn + 0.006 * p.nsets * (double)p.nbuckets_per_set + 11.0 * c * (p.nsets - 1);
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = p; }
   }
   return best;
@@ -44,7 +52,7 @@ int32_t g1_combine_dev(ctg_ctx* ctx, const G1XYZZ* d_in, uint32_t k, G1Affine* d
 }
 
 void msm_ws_free(MsmWorkspace& ws) {
-  void* ptrs[] = {ws.counts, ws.cursor, ws.entries, ws.buckets, ws.part_pt, ws.part_gb, ws.chunk, ws.result};
+  void* ptrs[] = {ws.counts, ws.cursor, ws.entries, ws.buckets, ws.part_pt, ws.part_gb, ws.chunk, ws.result, ws.tile_sums};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   ws = MsmWorkspace();

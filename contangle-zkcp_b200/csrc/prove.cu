@@ -121,7 +121,7 @@ template <class A>
 static int32_t make_bases(ctg_ctx* ctx, Bases& out, int group, uint64_t n, int copies, int c_bits) {
   out.group = group;
   out.n = n;
-  out.plan = msm_make_plan(n, copies, c_bits);
+  out.plan = msm_make_plan(n, copies, c_bits, sizeof(A));
   out.pts = nullptr;
   size_t bytes = (size_t)out.plan.copies * (n ? n : 1) * sizeof(A);
   cudaError_t e = cudaMalloc(&out.pts, bytes);

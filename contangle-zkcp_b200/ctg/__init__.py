@@ -185,25 +185,25 @@ class Context:
         self._check(load().ctg_ntt_fr_dev(self.h, C.c_void_p(d_ptr), C.c_uint32(log_n), int(inverse), int(coset)))
 
     # ---- bases / MSM
-    def bases_g1(self, points, copies=1, c_bits=0):
+    def bases_g1(self, points, copies=0, c_bits=0):
         points = _arr(points, G1_W)
         h = C.c_void_p()
         self._check(load().ctg_bases_upload_g1(self.h, _ptr(points), C.c_uint64(points.shape[0]), copies, c_bits, C.byref(h)))
         return Bases(self, h, 1)
 
-    def bases_g2(self, points, copies=1, c_bits=0):
+    def bases_g2(self, points, copies=0, c_bits=0):
         points = _arr(points, G2_W)
         h = C.c_void_p()
         self._check(load().ctg_bases_upload_g2(self.h, _ptr(points), C.c_uint64(points.shape[0]), copies, c_bits, C.byref(h)))
         return Bases(self, h, 2)
 
-    def bases_progression_g1(self, g, a_mont, b_mont, n, copies=1, c_bits=0):
+    def bases_progression_g1(self, g, a_mont, b_mont, n, copies=0, c_bits=0):
         g, a_mont, b_mont = _arr(g).reshape(G1_W), _arr(a_mont).reshape(FR_W), _arr(b_mont).reshape(FR_W)
         h = C.c_void_p()
         self._check(load().ctg_bases_progression_g1(self.h, _ptr(g), _ptr(a_mont), _ptr(b_mont), C.c_uint64(n), copies, c_bits, C.byref(h)))
         return Bases(self, h, 1)
 
-    def bases_progression_g2(self, g, a_mont, b_mont, n, copies=1, c_bits=0):
+    def bases_progression_g2(self, g, a_mont, b_mont, n, copies=0, c_bits=0):
         g, a_mont, b_mont = _arr(g).reshape(G2_W), _arr(a_mont).reshape(FR_W), _arr(b_mont).reshape(FR_W)
         h = C.c_void_p()
         self._check(load().ctg_bases_progression_g2(self.h, _ptr(g), _ptr(a_mont), _ptr(b_mont), C.c_uint64(n), copies, c_bits, C.byref(h)))
@@ -244,7 +244,7 @@ class Context:
         self._check(fn(self.h, C.c_void_p(d_partials), C.c_uint32(k), C.c_void_p(d_out_affine)))
 
     # ---- proving key / R1CS / prover
-    def upload_pk(self, pk: dict, num_instance, num_constraints, copies=1, c_bits=0):
+    def upload_pk(self, pk: dict, num_instance, num_constraints, copies=0, c_bits=0):
         """pk: dict of arrays alpha_g1, beta_g1, delta_g1, beta_g2, delta_g2, a_query, b_g1_query, b_g2_query, h_query, l_query."""
         v = PkView()
         keep = []

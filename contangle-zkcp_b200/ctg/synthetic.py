@@ -179,7 +179,7 @@ def progression_pk(ctx, r1cs, seed=0xC0FFEE):
     pk = {}
 
     def single(group, k):
-        b = (ctx.bases_progression_g1 if group == 1 else ctx.bases_progression_g2)(g1 if group == 1 else g2, fr_mont([k])[0], fr_mont([0])[0], 1)
+        b = (ctx.bases_progression_g1 if group == 1 else ctx.bases_progression_g2)(g1 if group == 1 else g2, fr_mont([k])[0], fr_mont([0])[0], 1, copies=1)
         out = b.download()[0]
         b.free()
         return out
@@ -188,7 +188,7 @@ def progression_pk(ctx, r1cs, seed=0xC0FFEE):
         a, b = dl[key]
         if count == 0:
             return np.zeros((0, 24 if group == 1 else 48), dtype=np.uint32)
-        t = (ctx.bases_progression_g1 if group == 1 else ctx.bases_progression_g2)(g1 if group == 1 else g2, fr_mont([a])[0], fr_mont([b])[0], count)
+        t = (ctx.bases_progression_g1 if group == 1 else ctx.bases_progression_g2)(g1 if group == 1 else g2, fr_mont([a])[0], fr_mont([b])[0], count, copies=1)
         out = t.download()
         t.free()
         return out

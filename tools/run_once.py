@@ -1,0 +1,42 @@
+"""Small driver for ncu captures: runs W warm-up + K measured invocations of one primitive.
+usage: python tools/run_once.py msm|msm2|ntt|prove LOG_N [copies] [c_bits]"""
+import os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "contangle-zkcp_b200")]
+import numpy as np
+import torch
+import ctg
+from ctg import synthetic as S
+
+what, lg = sys.argv[1], int(sys.argv[2])
+copies = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+c_bits = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+reps = int(os.environ.get("REPS", "2"))
+dev = torch.device("cuda", 0)
+ctx = ctg.Context(0, stream=torch.cuda.current_stream().cuda_stream)
+n = 1 << lg
+if what in ("msm", "msm2"):
+    gen = S.g1_gen_words() if what == "msm" else S.g2_gen_words()
+    mk = ctx.bases_progression_g1 if what == "msm" else ctx.bases_progression_g2
+    b = mk(gen, S.fr_mont([12345])[0], S.fr_mont([777])[0], n, copies=copies, c_bits=c_bits)
+    sc = torch.randint(0, 1 << 30, (n, 8), device=dev, dtype=torch.int32)
+    res = torch.zeros(96, dtype=torch.int32, device=dev)
+    for _ in range(reps):
+        ctx.msm_dev(b, sc.data_ptr(), n, res.data_ptr(), timed=True)
+        print(ctx.last_timings())
+elif what == "ntt":
+    x = torch.randint(0, 1 << 30, (n, 8), device=dev, dtype=torch.int32)
+    for _ in range(reps):
+        ctx.ntt_dev(x.data_ptr(), lg)
+    torch.cuda.synchronize()
+elif what == "prove":
+    r1cs, zm, _ = S.mul_chain(lg)
+    pk, _ = S.progression_pk(ctx, r1cs)
+    dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], copies=copies, c_bits=c_bits)
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
+    for _ in range(reps):
+        _, tm = ctx.prove(dpk, dr, zm, r, s, timed=True)
+        print(tm)
+torch.cuda.synchronize()
+print("done")
