@@ -1,0 +1,145 @@
+// ctg_groth16.hpp -- C++17 host-side mirror of the ark-groth16 0.3.0 prove API over the C ABI of
+// libctg_groth16.so (include/ctg_groth16.h).  The reference's host language is Rust (crates under ../rust,
+// source only: no Rust toolchain on the build box); this header is the compiled-language stand-in with the same
+// names, argument meaning and error behaviour:
+//
+//   ark_groth16::ProvingKey<Bls12_381>           -> ctg::ProvingKey            (host vectors, wire layout)
+//   (new) device residency of the key            -> ctg::DeviceProvingKey      (lib/src/zk/encryption.rs:22,31-32)
+//   ark_relations ConstraintMatrices             -> ctg::ConstraintMatrices    (rows of (coeff, column))
+//   ark_groth16::create_proof(circuit, pk, r, s) -> ctg::create_proof(dpk, cs, r, s)
+//   ark_groth16::create_random_proof(.., rng)    -> ctg::create_random_proof(dpk, cs, rng)   (r first, then s)
+//   ark_groth16::Proof<Bls12_381>                -> ctg::Proof { a, b, c }
+//   SynthesisError                               -> ctg::Error (std::runtime_error with the C ABI message)
+//
+// "cs" is the synthesized constraint system (matrices + full assignment): synthesis itself is circuit code and
+// stays with the caller, as it stays in Rust in the reference (circuits-ark/src/encryption.rs:303-317).
+// Header-only; link with -lctg_groth16.  No CPU fallback: Context's constructor throws without an sm_100 device.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/ctg_groth16.h"
+
+namespace ctg {
+
+struct Error : std::runtime_error { int32_t code; Error(int32_t c, const std::string& m) : std::runtime_error(m), code(c) {} };
+
+class Context {
+ public:
+  explicit Context(int device = 0) {
+    int32_t rc = ctg_ctx_create(&device, 1, &ctx_);
+    if (rc != CTG_OK) throw Error(rc, "ctg_ctx_create failed: no usable sm_100 CUDA device (there is no CPU fallback)");
+  }
+  ~Context() { ctg_ctx_destroy(ctx_); }
+  Context(const Context&) = delete;
+  Context& operator=(const Context&) = delete;
+  ctg_ctx* raw() const { return ctx_; }
+  void check(int32_t rc) const { if (rc != CTG_OK) throw Error(rc, ctg_last_error(ctx_)); }
+
+ private:
+  ctg_ctx* ctx_ = nullptr;
+};
+
+// ark_groth16::ProvingKey<Bls12_381>; points in the wire layout (Montgomery, x || y, all-zero = infinity)
+struct VerifyingKey {
+  ctg_g1_affine alpha_g1{};
+  ctg_g2_affine beta_g2{}, gamma_g2{}, delta_g2{};
+  std::vector<ctg_g1_affine> gamma_abc_g1;
+};
+struct ProvingKey {
+  VerifyingKey vk;
+  ctg_g1_affine beta_g1{}, delta_g1{};
+  std::vector<ctg_g1_affine> a_query, b_g1_query, h_query, l_query;
+  std::vector<ctg_g2_affine> b_g2_query;
+};
+struct Proof { ctg_g1_affine a; ctg_g2_affine b; ctg_g1_affine c; };
+
+// ark_relations::r1cs::ConstraintMatrices + the assignment of one synthesis run
+using Row = std::vector<std::pair<ctg_fr, size_t>>;  // (coefficient (Montgomery), column); columns: instance first, then witness
+struct ConstraintSystem {
+  size_t num_instance_variables = 1;  // includes the constant 1
+  size_t num_witness_variables = 0;
+  std::vector<Row> a, b, c;           // num_constraints rows each
+  std::vector<ctg_fr> instance_assignment, witness_assignment;
+  size_t num_constraints() const { return a.size(); }
+};
+
+class DeviceProvingKey {
+ public:
+  // num_instance / num_constraints: shape of the circuit the key was generated for
+  DeviceProvingKey(const Context& ctx, const ProvingKey& pk, size_t num_instance, size_t num_constraints, int copies = 0, int c_bits = 0)
+      : ctx_(ctx), ni_(num_instance), nc_(num_constraints) {
+    ctg_pk_view v{};
+    v.alpha_g1 = &pk.vk.alpha_g1; v.beta_g1 = &pk.beta_g1; v.delta_g1 = &pk.delta_g1;
+    v.beta_g2 = &pk.vk.beta_g2; v.delta_g2 = &pk.vk.delta_g2;
+    v.a_query = pk.a_query.data(); v.a_len = pk.a_query.size();
+    v.b_g1_query = pk.b_g1_query.data(); v.b_g1_len = pk.b_g1_query.size();
+    v.b_g2_query = pk.b_g2_query.data(); v.b_g2_len = pk.b_g2_query.size();
+    v.h_query = pk.h_query.data(); v.h_len = pk.h_query.size();
+    v.l_query = pk.l_query.data(); v.l_len = pk.l_query.size();
+    ctx_.check(ctg_pk_upload(ctx_.raw(), &v, num_instance, num_constraints, copies, c_bits, &pk_));
+  }
+  ~DeviceProvingKey() {
+    if (r1cs_) ctg_r1cs_free(ctx_.raw(), r1cs_);
+    ctg_pk_free(ctx_.raw(), pk_);
+  }
+  DeviceProvingKey(const DeviceProvingKey&) = delete;
+  DeviceProvingKey& operator=(const DeviceProvingKey&) = delete;
+
+  // R1CS matrices are per-circuit constants: uploaded with the first proof, reused afterwards.
+  const ctg_r1cs* r1cs_for(const ConstraintSystem& cs) {
+    if (cs.num_instance_variables != ni_ || cs.num_constraints() != nc_) throw Error(CTG_ERR_INVALID, "constraint system does not match the proving key");
+    if (r1cs_) return r1cs_;
+    struct Flat { std::vector<uint64_t> rp; std::vector<uint32_t> col; std::vector<ctg_fr> val; ctg_csr view; };
+    Flat f[3];
+    const std::vector<Row>* mats[3] = {&cs.a, &cs.b, &cs.c};
+    for (int k = 0; k < 3; k++) {
+      f[k].rp.push_back(0);
+      for (const Row& row : *mats[k]) {
+        for (const auto& e : row) { f[k].val.push_back(e.first); f[k].col.push_back((uint32_t)e.second); }
+        f[k].rp.push_back(f[k].col.size());
+      }
+      f[k].view = ctg_csr{f[k].rp.data(), f[k].col.data(), f[k].val.data()};
+    }
+    ctx_.check(ctg_r1cs_upload(ctx_.raw(), cs.num_instance_variables, cs.num_witness_variables, cs.num_constraints(), &f[0].view, &f[1].view,
+                               &f[2].view, &r1cs_));
+    return r1cs_;
+  }
+  const Context& ctx() const { return ctx_; }
+  const ctg_pk* raw() const { return pk_; }
+
+ private:
+  const Context& ctx_;
+  ctg_pk* pk_ = nullptr;
+  ctg_r1cs* r1cs_ = nullptr;
+  size_t ni_, nc_;
+};
+
+// ark_groth16::create_proof(circuit, pk, r, s) after synthesis
+inline Proof create_proof(DeviceProvingKey& pk, const ConstraintSystem& cs, const ctg_fr& r, const ctg_fr& s, ctg_timings* timings = nullptr) {
+  const ctg_r1cs* r1cs = pk.r1cs_for(cs);
+  if (cs.instance_assignment.size() != cs.num_instance_variables || cs.witness_assignment.size() != cs.num_witness_variables)
+    throw Error(CTG_ERR_INVALID, "AssignmentMissing");  // SynthesisError::AssignmentMissing
+  std::vector<ctg_fr> z;
+  z.reserve(cs.instance_assignment.size() + cs.witness_assignment.size());
+  z.insert(z.end(), cs.instance_assignment.begin(), cs.instance_assignment.end());
+  z.insert(z.end(), cs.witness_assignment.begin(), cs.witness_assignment.end());
+  ctg_proof out;
+  pk.ctx().check(ctg_prove(pk.ctx().raw(), pk.raw(), r1cs, z.data(), &r, &s, &out, timings));
+  return Proof{out.a, out.b, out.c};
+}
+
+// ark_groth16::create_random_proof: `rng()` must return one uniformly random Fr as a Montgomery image, as ark-ff's
+// Fr::rand does (rejection sampling of the image itself); it is called for r first, then for s.
+template <class Rng> inline Proof create_random_proof(DeviceProvingKey& pk, const ConstraintSystem& cs, Rng&& rng) {
+  const ctg_fr r = rng();
+  const ctg_fr s = rng();
+  return create_proof(pk, cs, r, s);
+}
+
+}  // namespace ctg

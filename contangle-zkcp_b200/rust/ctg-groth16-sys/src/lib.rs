@@ -1,0 +1,71 @@
+//! Raw binding of include/ctg_groth16.h.  One `extern "C"` item per declaration in the header; layouts are
+//! `#[repr(C)]` copies of the header's structs.  Nothing here is safe; see the `ctg-groth16` crate.
+#![allow(non_camel_case_types)]
+use std::os::raw::{c_char, c_int, c_void};
+
+pub const CTG_OK: i32 = 0;
+pub const CTG_ERR_INVALID: i32 = -1;
+pub const CTG_ERR_CUDA: i32 = -2;
+pub const CTG_ERR_OOM: i32 = -3;
+pub const CTG_ERR_STATE: i32 = -4;
+pub const CTG_SCALARS_CANONICAL: u32 = 0;
+pub const CTG_SCALARS_MONT: u32 = 1;
+pub const CTG_MSM_TIMED: u32 = 0x100;
+
+#[repr(C)] pub struct ctg_ctx { _p: [u8; 0] }
+#[repr(C)] pub struct ctg_bases { _p: [u8; 0] }
+#[repr(C)] pub struct ctg_pk { _p: [u8; 0] }
+#[repr(C)] pub struct ctg_r1cs { _p: [u8; 0] }
+
+/// ark-ff Fp256 memory image: [u64; 4] little-endian Montgomery limbs == [u32; 8]
+#[repr(C)] #[derive(Clone, Copy, Default)] pub struct ctg_fr { pub v: [u32; 8] }
+/// ark-ff Fp384 memory image
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_fq { pub v: [u32; 12] }
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_g1_affine { pub x: ctg_fq, pub y: ctg_fq }
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_g2_affine { pub x_c0: ctg_fq, pub x_c1: ctg_fq, pub y_c0: ctg_fq, pub y_c1: ctg_fq }
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_g1_xyzz { pub x: ctg_fq, pub y: ctg_fq, pub zz: ctg_fq, pub zzz: ctg_fq }
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_g2_xyzz { pub c: [ctg_fq; 8] }
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_proof { pub a: ctg_g1_affine, pub b: ctg_g2_affine, pub c: ctg_g1_affine }
+
+#[repr(C)]
+pub struct ctg_pk_view {
+    pub alpha_g1: *const ctg_g1_affine, pub beta_g1: *const ctg_g1_affine, pub delta_g1: *const ctg_g1_affine,
+    pub beta_g2: *const ctg_g2_affine, pub delta_g2: *const ctg_g2_affine,
+    pub a_query: *const ctg_g1_affine, pub a_len: u64,
+    pub b_g1_query: *const ctg_g1_affine, pub b_g1_len: u64,
+    pub b_g2_query: *const ctg_g2_affine, pub b_g2_len: u64,
+    pub h_query: *const ctg_g1_affine, pub h_len: u64,
+    pub l_query: *const ctg_g1_affine, pub l_len: u64,
+}
+#[repr(C)] pub struct ctg_csr { pub row_ptr: *const u64, pub col: *const u32, pub val: *const ctg_fr }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct ctg_timings {
+    pub h2d_ms: f32, pub witness_map_ms: f32, pub msm_h_ms: f32, pub msm_l_ms: f32, pub msm_a_ms: f32, pub msm_b_g1_ms: f32,
+    pub msm_b_g2_ms: f32, pub finalize_ms: f32, pub total_ms: f32, pub msm_sort_ms: f32, pub msm_accumulate_ms: f32, pub msm_reduce_ms: f32,
+}
+
+extern "C" {
+    pub fn ctg_ctx_create(device_ids: *const c_int, n_devices: c_int, out: *mut *mut ctg_ctx) -> i32;
+    pub fn ctg_ctx_destroy(ctx: *mut ctg_ctx);
+    pub fn ctg_last_error(ctx: *mut ctg_ctx) -> *const c_char;
+    pub fn ctg_ctx_set_stream(ctx: *mut ctg_ctx, cuda_stream: *mut c_void) -> i32;
+    pub fn ctg_sync(ctx: *mut ctg_ctx) -> i32;
+    pub fn ctg_launch_count(ctx: *mut ctg_ctx) -> u64;
+    pub fn ctg_last_timings(ctx: *mut ctg_ctx, out: *mut ctg_timings) -> i32;
+    pub fn ctg_ntt_fr(ctx: *mut ctg_ctx, host_data: *mut ctg_fr, log_n: u32, inverse: c_int, coset: c_int) -> i32;
+    pub fn ctg_bases_upload_g1(ctx: *mut ctg_ctx, pts: *const ctg_g1_affine, n: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_bases) -> i32;
+    pub fn ctg_bases_upload_g2(ctx: *mut ctg_ctx, pts: *const ctg_g2_affine, n: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_bases) -> i32;
+    pub fn ctg_bases_free(ctx: *mut ctg_ctx, bases: *mut ctg_bases);
+    pub fn ctg_msm_g1(ctx: *mut ctg_ctx, bases: *const ctg_bases, scalars: *const ctg_fr, n: u64, flags: u32, out: *mut ctg_g1_affine) -> i32;
+    pub fn ctg_msm_g2(ctx: *mut ctg_ctx, bases: *const ctg_bases, scalars: *const ctg_fr, n: u64, flags: u32, out: *mut ctg_g2_affine) -> i32;
+    pub fn ctg_pk_upload(ctx: *mut ctg_ctx, pk: *const ctg_pk_view, num_instance: u64, num_constraints: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_pk) -> i32;
+    pub fn ctg_pk_free(ctx: *mut ctg_ctx, pk: *mut ctg_pk);
+    pub fn ctg_r1cs_upload(ctx: *mut ctg_ctx, num_instance: u64, num_witness: u64, num_constraints: u64,
+                           a: *const ctg_csr, b: *const ctg_csr, c: *const ctg_csr, out: *mut *mut ctg_r1cs) -> i32;
+    pub fn ctg_r1cs_free(ctx: *mut ctg_ctx, r1cs: *mut ctg_r1cs);
+    pub fn ctg_witness_map(ctx: *mut ctg_ctx, r1cs: *const ctg_r1cs, z: *const ctg_fr, h_out: *mut ctg_fr) -> i32;
+    pub fn ctg_prove(ctx: *mut ctg_ctx, pk: *const ctg_pk, r1cs: *const ctg_r1cs, z: *const ctg_fr, r: *const ctg_fr, s: *const ctg_fr,
+                     out: *mut ctg_proof, timings: *mut ctg_timings) -> i32;
+    pub fn ctg_prove_batch(ctx: *mut ctg_ctx, pk: *const ctg_pk, r1cs: *const ctg_r1cs, n_proofs: u32, z_batch: *const ctg_fr,
+                           rs_batch: *const ctg_fr, out: *mut ctg_proof) -> i32;
+}
