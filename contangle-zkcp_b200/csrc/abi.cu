@@ -13,7 +13,11 @@ namespace ctg {
 int32_t field_op_dev(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n, cudaStream_t st);
 size_t field_elem_bytes(int field);
 int32_t imad_probe(ctg_ctx* ctx, double* imad_per_s, double* fq_mul_per_s);
-int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, ctg_pk** out);
+int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, int shard_index, int shard_count, ctg_pk** out);
+int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch, ctg_proof* out);
+int32_t prove_partial(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, void* out_partials, ctg_timings* tm);
+int32_t prove_combine(ctg_ctx* ctx, const void* host_partials, uint32_t k, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out);
+void lanes_destroy(ctg_ctx* ctx);
 void pk_free(ctg_pk* pk);
 int32_t r1cs_upload(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, const ctg_csr* const mats[3], ctg_r1cs** out);
 void r1cs_free(ctg_r1cs* r);
@@ -114,6 +118,7 @@ void ctg_ctx_destroy(ctg_ctx* ctx) {
   for (auto& kv : ctx->domains) {
     cudaFree(kv.second.tw_fwd); cudaFree(kv.second.tw_inv); cudaFree(kv.second.gpow); cudaFree(kv.second.gpow_n); cudaFree(kv.second.gipow_n);
   }
+  lanes_destroy(ctx);
   for (auto& w : ctx->ws) msm_ws_free(w);
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
@@ -216,7 +221,7 @@ int32_t ctg_ntt_fr(ctg_ctx* ctx, ctg_fr* host_data, uint32_t log_n, int inverse,
 // ---- bases ------------------------------------------------------------------------------------
 static int32_t bases_new(ctg_ctx* ctx, int group, uint64_t n, int copies, int c_bits, ctg_bases** out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
-  if (c_bits != 0 && (c_bits < 2 || c_bits > 16)) return fail(ctx, CTG_ERR_INVALID, "bases: c_bits must be 0 or in [2, 16]");
+  if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "bases: c_bits must be 0 or in [2, 21]");
   if (copies < 0) return fail(ctx, CTG_ERR_INVALID, "bases: copies must be >= 0");
   ctg_bases* h = new ctg_bases();
   h->b.group = group;
@@ -342,8 +347,14 @@ int32_t ctg_g2_combine(ctg_ctx* ctx, const ctg_g2_xyzz* host_partials, uint32_t 
 // ---- proving key / R1CS / prover --------------------------------------------------------------
 int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits, ctg_pk** out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
-  if (c_bits != 0 && (c_bits < 2 || c_bits > 16)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 16]");
-  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, out);
+  if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 21]");
+  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, 0, 1, out);
+}
+int32_t ctg_pk_upload_shard(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
+                            int shard_index, int shard_count, ctg_pk** out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 21]");
+  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, shard_index, shard_count, out);
 }
 void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk) {
   if (ctx) cudaStreamSynchronize(ctx->stream);
@@ -378,10 +389,19 @@ int32_t ctg_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, const ct
 int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch,
                         ctg_proof* out) {
   if (!ctx || !pk || !r1cs || !z_batch || !rs_batch || !out) return ctx ? fail(ctx, CTG_ERR_INVALID, "prove_batch: null argument") : CTG_ERR_INVALID;
-  const uint64_t m = pk_num_vars(pk);
-  for (uint32_t i = 0; i < n_proofs; i++)
-    CTG_TRY(prove(ctx, pk, r1cs, z_batch + (size_t)i * m, rs_batch + 2 * (size_t)i, rs_batch + 2 * (size_t)i + 1, out + i, nullptr));
-  return CTG_OK;
+  return prove_batch(ctx, pk, r1cs, n_proofs, z_batch, rs_batch, out);
+}
+int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
+                          ctg_proof_partial* out, ctg_timings* timings) {
+  if (!ctx) return CTG_ERR_INVALID;
+  ctg_timings local;
+  int32_t rc = prove_partial(ctx, pk_shard, r1cs, z, r, s, out, timings ? &local : nullptr);
+  if (rc == CTG_OK && timings) { *timings = local; g_last_timings = local; }
+  return rc;
+}
+int32_t ctg_prove_combine(ctg_ctx* ctx, const ctg_proof_partial* partials, uint32_t k, const ctg_fr* r, const ctg_fr* s, ctg_proof* out) {
+  if (!ctx) return CTG_ERR_INVALID;
+  return prove_combine(ctx, partials, k, r, s, out);
 }
 
 }  // extern "C"

@@ -57,6 +57,20 @@ struct Bases {  // device-resident base table (a proving-key query or a standalo
 
 }  // namespace ctg
 
+namespace ctg {
+// One in-flight proof: 5 streams (0 = witness map + H MSM, 1..4 = L, A, B1, B2 MSMs), one MSM workspace per stream,
+// private scratch.  Lane 0's stream 0 is the context stream.  Batched proving round-robins over the lanes.
+struct ProveLane {
+  bool ready = false;
+  cudaStream_t st[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  MsmWorkspace ws[5];
+  void* scratch = nullptr; size_t scratch_bytes = 0;
+  cudaEvent_t ev_z = nullptr, ev_done[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_t[16];   // stage timers
+};
+static constexpr int kMaxLanes = 4;
+}  // namespace ctg
+
 struct ctg_ctx {
   int device = 0;
   int sm_count = 148;
@@ -66,6 +80,8 @@ struct ctg_ctx {
   uint64_t launches = 0;
   std::map<int, ctg::NttDomain> domains;
   ctg::MsmWorkspace ws[2];
+  ctg::ProveLane lanes[ctg::kMaxLanes];
+  void* pinned_proofs = nullptr; size_t pinned_proofs_bytes = 0;
   void* scratch = nullptr; size_t scratch_bytes = 0;     // general device scratch (staging)
   void* pinned = nullptr; size_t pinned_bytes = 0;       // pinned host staging
   cudaEvent_t ev[16];

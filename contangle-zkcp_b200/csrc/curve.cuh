@@ -34,7 +34,7 @@ template <class F> CTG_HD_COLD XYZZ<F> xyzz_dbl_affine(const Affine<F>& p) {
   F xx = p.x.sqr(), M = xx.dbl() + xx;
   XYZZ<F> r;
   r.X = M.sqr() - S.dbl();
-  r.Y = M * (S - r.X) - W * p.y;
+  r.Y = F::mul2_sub(M, S - r.X, W, p.y);
   r.ZZ = V;
   r.ZZZ = W;
   return r;
@@ -47,7 +47,7 @@ template <class F> CTG_HD_COLD XYZZ<F> xyzz_dbl(const XYZZ<F>& p) {
   F xx = p.X.sqr(), M = xx.dbl() + xx;
   XYZZ<F> r;
   r.X = M.sqr() - S.dbl();
-  r.Y = M * (S - r.X) - W * p.Y;
+  r.Y = F::mul2_sub(M, S - r.X, W, p.Y);
   r.ZZ = V * p.ZZ;
   r.ZZZ = W * p.ZZZ;
   return r;
@@ -69,7 +69,7 @@ template <class F> CTG_HD XYZZ<F> xyzz_madd(const XYZZ<F>& acc, const Affine<F>&
   F PP = P.sqr(), PPP = P * PP, Q = acc.X * PP;
   XYZZ<F> r;
   r.X = R.sqr() - PPP - Q.dbl();
-  r.Y = R * (Q - r.X) - acc.Y * PPP;
+  r.Y = F::mul2_sub(R, Q - r.X, acc.Y, PPP);  // one reduction for the two products
   r.ZZ = acc.ZZ * PP;
   r.ZZZ = acc.ZZZ * PPP;
   return r;
@@ -88,7 +88,7 @@ template <class F> CTG_HD_COLD XYZZ<F> xyzz_add(const XYZZ<F>& a, const XYZZ<F>&
   F PP = P.sqr(), PPP = P * PP, Q = U1 * PP;
   XYZZ<F> r;
   r.X = R.sqr() - PPP - Q.dbl();
-  r.Y = R * (Q - r.X) - S1 * PPP;
+  r.Y = F::mul2_sub(R, Q - r.X, S1, PPP);
   r.ZZ = a.ZZ * b.ZZ * PP;
   r.ZZZ = a.ZZZ * b.ZZZ * PPP;
   return r;

@@ -154,6 +154,82 @@ template <class P> struct alignas(16) Fp {
     O[N - 1] = ptx::addc(O[N - 1], 0);
   }
 
+  // E/O += x * y without re-alignment (same limb tiling as redc_row); used by sum-of-products rows
+  CTG_HD static void acc_row(uint32_t* E, uint32_t* O, const uint32_t* x, uint32_t y) {
+    O[0] = ptx::mad_lo_cc(x[1], y, O[0]);
+    O[1] = ptx::madc_hi_cc(x[1], y, O[1]);
+#pragma unroll
+    for (int j = 3; j < N; j += 2) {
+      O[j - 1] = ptx::madc_lo_cc(x[j], y, O[j - 1]);
+      if (j == N - 1) O[j] = ptx::madc_hi(x[j], y, O[j]);
+      else O[j] = ptx::madc_hi_cc(x[j], y, O[j]);
+    }
+    E[0] = ptx::mad_lo_cc(x[0], y, E[0]);
+    E[1] = ptx::madc_hi_cc(x[0], y, E[1]);
+#pragma unroll
+    for (int j = 2; j < N; j += 2) {
+      E[j] = ptx::madc_lo_cc(x[j], y, E[j]);
+      E[j + 1] = ptx::madc_hi_cc(x[j], y, E[j + 1]);
+    }
+    O[N - 1] = ptx::addc(O[N - 1], 0);
+  }
+
+  // (sum_k a[k] * b[k]) / R mod p with ONE Montgomery reduction ("lazy reduction"): every row adds the K partial
+  // products before the reduction step.  Needs (K + 1) * p < 2^(32 N) so that the running sum fits its limbs and
+  // p * (1 + K p / R) < 2p for the single final subtraction: true for Fq (p / R ~ 0.10) up to K = 8, not for Fr.
+  template <int K> CTG_HD static Fp dot(const Fp* const* a, const Fp* const* b) {
+    static_assert(N == 12 && K >= 1 && K <= 8, "lazy sums of products are only safe for the 381-bit field");
+    uint32_t ev[N], od[N];
+#pragma unroll
+    for (int j = 0; j < N; j += 2) {
+      ev[j] = ptx::mul_lo(a[0]->v[j], b[0]->v[0]);
+      ev[j + 1] = ptx::mul_hi(a[0]->v[j], b[0]->v[0]);
+      od[j] = ptx::mul_lo(a[0]->v[j + 1], b[0]->v[0]);
+      od[j + 1] = ptx::mul_hi(a[0]->v[j + 1], b[0]->v[0]);
+    }
+#pragma unroll
+    for (int k = 1; k < K; k++) acc_row(ev, od, a[k]->v, b[k]->v[0]);
+    redc_row(ev, od);
+#pragma unroll
+    for (int i = 1; i < N; i += 2) {
+      mad_row(od, ev, a[0]->v, b[0]->v[i]);
+#pragma unroll
+      for (int k = 1; k < K; k++) acc_row(od, ev, a[k]->v, b[k]->v[i]);
+      redc_row(od, ev);
+      if (i + 1 < N) {
+        mad_row(ev, od, a[0]->v, b[0]->v[i + 1]);
+#pragma unroll
+        for (int k = 1; k < K; k++) acc_row(ev, od, a[k]->v, b[k]->v[i + 1]);
+        redc_row(ev, od);
+      }
+    }
+    Fp r;
+    r.v[0] = ptx::add_cc(ev[0], od[1]);
+#pragma unroll
+    for (int k = 1; k < N - 1; k++) r.v[k] = ptx::addc_cc(ev[k], od[k + 1]);
+    r.v[N - 1] = ptx::addc(ev[N - 1], 0);
+    reduce_once(r.v);
+    return r;
+  }
+  // a*b + c*d and a*b - c*d with one reduction (p - d stands in for -d; d = 0 gives p, still within the bounds)
+  CTG_HD static Fp mul2_add(const Fp& a, const Fp& b, const Fp& c, const Fp& d) {
+    const Fp* x[2] = {&a, &c};
+    const Fp* y[2] = {&b, &d};
+    return dot<2>(x, y);
+  }
+  CTG_HD Fp neg_lazy() const {  // p - x in [1, p]
+    Fp r;
+    r.v[0] = ptx::sub_cc(P::mod(0), v[0]);
+#pragma unroll
+    for (int i = 1; i < N - 1; i++) r.v[i] = ptx::subc_cc(P::mod(i), v[i]);
+    r.v[N - 1] = ptx::subc(P::mod(N - 1), v[N - 1]);
+    return r;
+  }
+  CTG_HD static Fp mul2_sub(const Fp& a, const Fp& b, const Fp& c, const Fp& d) {
+    const Fp nd = d.neg_lazy();
+    return mul2_add(a, b, c, nd);
+  }
+
   CTG_HD friend Fp operator*(const Fp& a, const Fp& b) {
     uint32_t ev[N], od[N];
 #pragma unroll
@@ -224,10 +300,18 @@ struct Fq2 {
   CTG_HD friend Fq2 operator-(const Fq2& a, const Fq2& b) { return {a.c0 - b.c0, a.c1 - b.c1}; }
   CTG_HD Fq2 neg() const { return {c0.neg(), c1.neg()}; }
   CTG_HD Fq2 dbl() const { return {c0.dbl(), c1.dbl()}; }
+  // schoolbook with lazy reduction: 4 products, 2 reductions, one negation
   CTG_HD friend Fq2 operator*(const Fq2& a, const Fq2& b) {
-    Fq v0 = a.c0 * b.c0, v1 = a.c1 * b.c1;
-    Fq s = (a.c0 + a.c1) * (b.c0 + b.c1);
-    return {v0 - v1, s - v0 - v1};
+    return {Fq::mul2_sub(a.c0, b.c0, a.c1, b.c1), Fq::mul2_add(a.c0, b.c1, a.c1, b.c0)};
+  }
+  // a*b - c*d over Fq2: 8 products, 2 reductions
+  CTG_HD static Fq2 mul2_sub(const Fq2& a, const Fq2& b, const Fq2& c, const Fq2& d) {
+    // c0 = a0 b0 - a1 b1 - c0 d0 + c1 d1 ; c1 = a0 b1 + a1 b0 - c0 d1 - c1 d0
+    const Fq nb1 = b.c1.neg_lazy(), nd0 = d.c0.neg_lazy(), nd1 = d.c1.neg_lazy();
+    const Fq* x0[4] = {&a.c0, &a.c1, &c.c0, &c.c1};
+    const Fq* y0[4] = {&b.c0, &nb1, &nd0, &d.c1};
+    const Fq* y1[4] = {&b.c1, &b.c0, &nd1, &nd0};
+    return {Fq::dot<4>(x0, y0), Fq::dot<4>(x0, y1)};
   }
   CTG_HD Fq2 sqr() const {
     Fq t = c0 * c1;

@@ -12,8 +12,8 @@
 //                    emits a bucket sum whenever the bucket id changes.  Work per thread is
 //                    identical whatever the scalar distribution (zeros, ones, bytes, uniform).
 //   5. msm_fixup     buckets cut by a slice boundary: their partial sums are added by one warp each
-//   6. msm_bucket_reduce  sum_b (b+1) * bucket[b] with chunked running sums, all chunks in parallel
-//   7. msm_set_sum / msm_horner  per-set totals, then sum_g 2^(c g) S_g
+//   6. msm_halve x log2(B), msm_reduce_final   sum_b (b+1) * bucket[b] by halving trees of minimal serial depth
+//   7. msm_horner  sum_g 2^(c g) S_g over the bucket sets (skipped when there is one set)
 // Windows w = j * G + g use the precomputed multiple 2^(c G j) * P (copy j of the base table),
 // so only G = ceil(W / copies) bucket sets exist; with copies = W there is a single set and no
 // doubling chain at the end.
@@ -252,73 +252,85 @@ template <class F> __global__ void __launch_bounds__(64) msm_fixup_kernel(const 
 }
 
 // ---- 6. bucket reduction ----------------------------------------------------------------------
-// grid = (blocks per set, nsets); each thread owns L consecutive buckets.
-template <class F, int TB> __global__ void __launch_bounds__(TB) msm_bucket_reduce_kernel(const XYZZ<F>* __restrict__ buckets, uint32_t B, int L,
-                                                                                         XYZZ<F>* chunk_out) {
-  __shared__ XYZZ<F> sh[TB];
+// S = sum_b (b + 1) * B[b] over the 2^(c-1) buckets of a set.  A single group operation has a latency of ~15-20 us
+// (14 dependent 381-bit products on one thread), so the reduction is organised for minimal SERIAL DEPTH:
+//   S = total + sum_k 2^k * O_k,   O_k = sum of the odd-indexed items of B^(k),   B^(k+1)[i] = B^(k)[2i] + B^(k)[2i+1]
+// (because sum_b b B[b] = 2 * sum_i i B'[i] + sum of odd items).  One launch of msm_halve_kernel performs one halving
+// step of the main array AND of every O_k tree that already exists, so after log2(N) + 1 launches every O_k and the
+// total are known; msm_reduce_final_kernel then lets thread k double O_k k times and tree-adds the results.
+// Depth: log2(N) + 1 additions, <= c - 2 doublings, 5 additions -- instead of the O(L * levels) of running sums.
+// Sets with more than 2^16 buckets are first shrunk by msm_reduce_chunk_kernel (running sums over chunks of L = 2^logL
+// buckets, throughput-bound): sum_b b B[b] = sum_t wt_t + L * sum_t t run_t.
+template <class F, int TB> __global__ void __launch_bounds__(TB) msm_reduce_chunk_kernel(const XYZZ<F>* __restrict__ items, uint64_t set_stride, int logL,
+                                                                                        XYZZ<F>* run_out, XYZZ<F>* wt_out, uint32_t T) {
   const uint32_t set = blockIdx.y;
-  const uint32_t ch = blockIdx.x * TB + threadIdx.x;
-  const uint64_t off = (uint64_t)ch * L;
+  const uint32_t t = blockIdx.x * TB + threadIdx.x;
+  if (t >= T) return;
+  const XYZZ<F>* it = items + (uint64_t)set * set_stride + ((uint64_t)t << logL);
   XYZZ<F> run = XYZZ<F>::inf(), wt = XYZZ<F>::inf();
-  if (off < B) {
-    for (int i = L - 1; i >= 0; i--) {
-      const uint64_t bidx = off + i;
-      if (bidx < B) {
-        XYZZ<F> o;
-        copy16(o, buckets[(uint64_t)set * B + bidx]);
-        run = xyzz_add(run, o);
-      }
-      wt = xyzz_add(wt, run);
-    }
-    // wt = sum (b - off + 1) * bucket[b];  add off * run
-    if (off != 0 && !run.is_inf()) {
-      XYZZ<F> m = XYZZ<F>::inf();
-      uint32_t o32 = (uint32_t)off;
-      for (int bit = 31 - __clz(o32); bit >= 0; bit--) {
-        m = xyzz_dbl(m);
-        if ((o32 >> bit) & 1) m = xyzz_add(m, run);
-      }
-      wt = xyzz_add(wt, m);
-    }
-  }
-  copy16(sh[threadIdx.x], wt);
-  __syncthreads();
-  for (int s = TB / 2; s >= 1; s >>= 1) {
-    if ((int)threadIdx.x < s) {
-      XYZZ<F> o;
-      copy16(o, sh[threadIdx.x + s]);
-      wt = xyzz_add(wt, o);
-      copy16(sh[threadIdx.x], wt);
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) copy16(chunk_out[(uint64_t)set * gridDim.x + blockIdx.x], wt);
-}
-
-// ---- 7. per-set totals and window combine -----------------------------------------------------
-// one CTA per set: sums `per_set` chunk results
-template <class F, int TB> __global__ void __launch_bounds__(TB) msm_set_sum_kernel(const XYZZ<F>* chunk, uint32_t per_set, XYZZ<F>* set_out) {
-  __shared__ XYZZ<F> sh[TB];
-  XYZZ<F> acc = XYZZ<F>::inf();
-  for (uint32_t i = threadIdx.x; i < per_set; i += TB) {
+  for (int j = (1 << logL) - 1; j >= 1; j--) {   // wt = sum_j j * item[j]
     XYZZ<F> o;
-    copy16(o, chunk[(uint64_t)blockIdx.x * per_set + i]);
-    acc = xyzz_add(acc, o);
+    copy16(o, it[j]);
+    run = xyzz_add(run, o);
+    wt = xyzz_add(wt, run);
   }
-  copy16(sh[threadIdx.x], acc);
-  __syncthreads();
-  for (int s = TB / 2; s >= 1; s >>= 1) {
-    if ((int)threadIdx.x < s) {
-      XYZZ<F> o;
-      copy16(o, sh[threadIdx.x + s]);
-      acc = xyzz_add(acc, o);
-      copy16(sh[threadIdx.x], acc);
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) copy16(set_out[blockIdx.x], acc);
+  XYZZ<F> o;
+  copy16(o, it[0]);
+  run = xyzz_add(run, o);
+  copy16(run_out[(uint64_t)set * T + t], run);
+  copy16(wt_out[(uint64_t)set * T + t], wt);
 }
 
+static constexpr int kMaxHalveSegs = 24;
+struct HalveSeg {
+  const void* src;
+  void* dst;
+  uint32_t src_set_stride, dst_set_stride;  // in points
+  uint32_t step, off;                       // operands: src[(2i) * step + off], src[(2i + 1) * step + off]
+  uint32_t out_count, first_thread;
+  uint32_t copy;                            // 1: dst[0] = src[off] (a tree that starts with a single item)
+};
+struct HalveArgs { int nseg; HalveSeg s[kMaxHalveSegs]; };
+
+template <class F> __global__ void __launch_bounds__(64) msm_halve_kernel(HalveArgs a) {
+  const uint32_t t = blockIdx.x * 64 + threadIdx.x;
+  const uint32_t set = blockIdx.y;
+  int k = -1;
+#pragma unroll 1
+  for (int i = 0; i < a.nseg; i++)
+    if (t >= a.s[i].first_thread && t - a.s[i].first_thread < a.s[i].out_count) k = i;
+  if (k < 0) return;
+  const HalveSeg& s = a.s[k];
+  const uint32_t i = t - s.first_thread;
+  const XYZZ<F>* src = reinterpret_cast<const XYZZ<F>*>(s.src) + (uint64_t)set * s.src_set_stride;
+  XYZZ<F>* dst = reinterpret_cast<XYZZ<F>*>(s.dst) + (uint64_t)set * s.dst_set_stride;
+  XYZZ<F> x;
+  copy16(x, src[(uint64_t)(2 * i) * s.step + s.off]);
+  if (!s.copy) {
+    XYZZ<F> y;
+    copy16(y, src[(uint64_t)(2 * i + 1) * s.step + s.off]);
+    x = xyzz_add(x, y);
+  }
+  copy16(dst[i], x);
+}
+
+// finals[set][slot]: slot j < nplain are added as they are; slot nplain + k is doubled (k + shift) times first.
+template <class F> __global__ void __launch_bounds__(32) msm_reduce_final_kernel(const XYZZ<F>* finals, int nslots, int nplain, int shift, XYZZ<F>* set_out) {
+  __shared__ XYZZ<F> sh[32];
+  const unsigned lane = threadIdx.x;
+  XYZZ<F> acc = XYZZ<F>::inf();
+  if ((int)lane < nslots) {
+    copy16(acc, finals[(uint64_t)blockIdx.x * nslots + lane]);
+    if ((int)lane >= nplain && !acc.is_inf()) {
+      const int d = (int)lane - nplain + shift;
+      for (int i = 0; i < d; i++) acc = xyzz_dbl(acc);
+    }
+  }
+  acc = warp_sum(acc, sh, lane);
+  if (lane == 0) copy16(set_out[blockIdx.x], acc);
+}
+
+// ---- 7. window combine --------------------------------------------------------------------------
 // sum_g 2^(c g) S_g, single thread (G - 1) * c doublings; G = 1 when every window is precomputed
 template <class F> __global__ void msm_horner_kernel(const XYZZ<F>* sets, int nsets, int c, XYZZ<F>* out) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -431,8 +443,6 @@ template <class F, int MAXC> __global__ void __launch_bounds__(128) precompute_k
 
 // ---- host orchestration -------------------------------------------------------------------------
 template <class F> struct MsmHost {
-  static constexpr int kReduceTB = 64;
-  static constexpr int kReduceL = 8;
 
   static int32_t ensure_ws(ctg_ctx* ctx, MsmWorkspace& ws, const MsmPlan& plan, uint64_t n, int max_threads) {
     const size_t nb = (size_t)plan.nsets * plan.nbuckets_per_set;
@@ -463,7 +473,9 @@ template <class F> struct MsmHost {
       CTG_CUDA(ctx, cudaMalloc(&ws.part_gb, (size_t)2 * max_threads * sizeof(uint32_t)));
       ws.cap_part_bytes = pb;
     }
-    const size_t cb = (nb / kReduceL / kReduceTB + 2 * (size_t)plan.nsets + 64) * sizeof(XYZZ<F>);
+    // reduction scratch: chunk sums (2 * 2^16) + halving trees (main, weights, O_k: < 4 N points in all) per set
+    const size_t red_n = plan.nbuckets_per_set > 65536u ? 65536u : plan.nbuckets_per_set;
+    const size_t cb = ((size_t)plan.nsets * (6 * red_n + 64) + 256) * sizeof(XYZZ<F>);
     if (cb > ws.cap_chunk_bytes) {
       if (ws.chunk) cudaFree(ws.chunk);
       CTG_CUDA(ctx, cudaMalloc(&ws.chunk, cb));
@@ -533,17 +545,79 @@ template <class F> struct MsmHost {
     CTG_KERNEL_CHECK(ctx);
     if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
 
-    const uint32_t B = plan.nbuckets_per_set;
-    const uint32_t chunks = (B + kReduceL - 1) / kReduceL;
-    const uint32_t bps = (chunks + kReduceTB - 1) / kReduceTB;
-    dim3 grid(bps, plan.nsets);
-    msm_bucket_reduce_kernel<F, kReduceTB><<<grid, kReduceTB, 0, st>>>(buckets, B, kReduceL, chunk);
-    CTG_KERNEL_CHECK(ctx);
-    XYZZ<F>* set_out = chunk + (size_t)bps * plan.nsets;
-    msm_set_sum_kernel<F, 64><<<plan.nsets, 64, 0, st>>>(chunk, bps, set_out);
-    CTG_KERNEL_CHECK(ctx);
-    msm_horner_kernel<F><<<1, 32, 0, st>>>(set_out, plan.nsets, plan.c, d_out);
-    CTG_KERNEL_CHECK(ctx);
+    // bucket reduction (see section 6)
+    {
+      const int nsets = plan.nsets;
+      XYZZ<F>* pool = chunk;   // bump allocator over the reduction scratch, in points
+      size_t used = 0;
+      auto take = [&](size_t pts) { XYZZ<F>* p = pool + used; used += pts * (size_t)nsets; return p; };
+      const XYZZ<F>* cur = buckets;
+      uint32_t cur_stride = plan.nbuckets_per_set, N = plan.nbuckets_per_set;
+      int shift = 0;
+      const XYZZ<F>* wt_src = nullptr;
+      uint32_t wt_count = 0;
+      if (N > (1u << 16)) {   // shrink to 2^16 items with chunked running sums
+        shift = 0;
+        while ((N >> shift) > (1u << 16)) shift++;
+        const uint32_t T = N >> shift;
+        XYZZ<F>* run = take(T);
+        XYZZ<F>* wt = take(T);
+        msm_reduce_chunk_kernel<F, 64><<<dim3((T + 63) / 64, nsets), 64, 0, st>>>(cur, cur_stride, shift, run, wt, T);
+        CTG_KERNEL_CHECK(ctx);
+        cur = run; cur_stride = T; N = T;
+        wt_src = wt; wt_count = T;
+      }
+      // slots: 0 = total, 1 = sum of chunk weights (or infinity), 2 + k = O_k
+      int nO = 0;
+      while ((1u << nO) < N) nO++;          // log2(N): O_0 .. O_{log2 N - 1}
+      const int nslots = 2 + nO;
+      if (nslots > 32) return fail(ctx, CTG_ERR_STATE, "msm: too many reduction slots");
+      XYZZ<F>* finals = take(nslots);
+      CTG_CUDA(ctx, cudaMemsetAsync(finals, 0, (size_t)nslots * nsets * sizeof(XYZZ<F>), st));
+      struct Tree { const XYZZ<F>* src; uint32_t stride, count, step, off; int slot; };
+      std::vector<Tree> trees;
+      trees.push_back({cur, cur_stride, N, 1, 0, 0});                       // main array -> total
+      if (wt_src) trees.push_back({wt_src, wt_count, wt_count, 1, 0, 1});   // plain sum of the chunk weights
+      int next_O = 0;
+      while (!trees.empty()) {
+        HalveArgs args{};
+        uint32_t threads = 0;
+        std::vector<Tree> next;
+        for (Tree& tr : trees) {
+          if (args.nseg >= kMaxHalveSegs) return fail(ctx, CTG_ERR_STATE, "msm: too many reduction segments");
+          HalveSeg& sg = args.s[args.nseg++];
+          sg.src = tr.src; sg.src_set_stride = tr.stride; sg.step = tr.step; sg.off = tr.off; sg.first_thread = threads;
+          if (tr.count == 1) {            // single item: copy it to its slot
+            sg.copy = 1; sg.out_count = 1; sg.dst = finals + tr.slot; sg.dst_set_stride = nslots;
+          } else {
+            sg.copy = 0; sg.out_count = tr.count / 2;
+            if (sg.out_count == 1) { sg.dst = finals + tr.slot; sg.dst_set_stride = nslots; }
+            else {
+              XYZZ<F>* d = take(sg.out_count);
+              sg.dst = d; sg.dst_set_stride = sg.out_count;
+              next.push_back({d, sg.out_count, sg.out_count, 1, 0, tr.slot});
+            }
+          }
+          threads += sg.out_count;
+          // the main array spawns the tree of the odd items of the level it is reading now
+          if (tr.slot == 0 && tr.count >= 2) {
+            next.push_back({tr.src, tr.stride, tr.count / 2, 2 * tr.step, tr.off + tr.step, 2 + next_O});
+            next_O++;
+          }
+        }
+        if ((used + 64) * sizeof(XYZZ<F>) > ws.cap_chunk_bytes) return fail(ctx, CTG_ERR_STATE, "msm: reduction scratch too small");
+        msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
+        CTG_KERNEL_CHECK(ctx);
+        trees.swap(next);
+      }
+      XYZZ<F>* set_out = nsets == 1 ? d_out : take(1);
+      msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
+      CTG_KERNEL_CHECK(ctx);
+      if (nsets > 1) {
+        msm_horner_kernel<F><<<1, 32, 0, st>>>(set_out, nsets, plan.c, d_out);
+        CTG_KERNEL_CHECK(ctx);
+      }
+    }
     if (timed) {
       CTG_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
       CTG_CUDA(ctx, cudaEventSynchronize(ctx->ev[3]));

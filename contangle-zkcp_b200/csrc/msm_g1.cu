@@ -7,16 +7,17 @@ namespace ctg {
 
 // Plan selection.  Cost model in microseconds, constants measured on B200 (profiles/r01_*):
 //   bucket accumulation   windows * n mixed additions at ~2.5 G/s,
-//   bucket reduction      ~6 ns per bucket (two full additions + chunk offsets, latency-bound),
-//   window combine        c * (sets - 1) sequential doublings at ~11 us each (one thread),
-// Windows are signed, so c bits need 2^(c-1) buckets; c <= 16 keeps a bucket set at 2^15 entries.
+//   bucket reduction      halving trees: ~(c + 1) dependent additions + (c - 2) doublings at 12-20 us each (latency-bound),
+//                         plus a throughput term when a set has more than 2^16 buckets (chunked running sums first),
+//   window combine        c * (sets - 1) sequential doublings at ~12 us each (one thread).
+// Windows are signed, so c bits need 2^(c-1) buckets.  c <= 21 keeps the bucket-index scan within 1023 tiles.
 // copies_wanted = 0: keep as many precomputed multiples 2^(c G j) P as fit a 12 GiB table.
 MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes) {
   MsmPlan best{};
   double best_cost = -1;
   const double budget = 12.0 * 1024 * 1024 * 1024;
   const uint64_t nn = n ? n : 1;
-  for (int c = 2; c <= 16; c++) {
+  for (int c = 2; c <= 21; c++) {
     if (c_override > 0 && c != c_override) continue;
     MsmPlan p;
     p.c = c;
@@ -25,10 +26,14 @@ MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t poin
     if (cap > 32) cap = 32;  // precompute_kernel keeps at most 32 multiples per base
     while ((uint64_t)cap * nn >= (1ull << 31) && cap > 1) cap--;
     p.copies = copies_wanted <= 0 ? cap : std::min(copies_wanted, p.nwin);
+    if (p.copies > 32) p.copies = 32;
     p.nsets = (p.nwin + p.copies - 1) / p.copies;
     p.copies = (p.nwin + p.nsets - 1) / p.nsets;  // drop copies no window would use
     p.nbuckets_per_set = 1u << (c - 1);
-    double cost = 0.0004 * p.nwin * (double)nn + 0.006 * p.nsets * (double)p.nbuckets_per_set + 11.0 * c * (p.nsets - 1);
+    const double nb = (double)p.nsets * p.nbuckets_per_set;
+    if (c_override <= 0 && (nb > 2097152.0 || (double)nn * p.nwin >= 4294967296.0)) continue;
+    const double red = p.nbuckets_per_set > 65536u ? 0.0012 * nb : 0.0003 * nb;   // chunked running sums only above 2^16 buckets per set
+    double cost = 0.0004 * p.nwin * (double)nn + red + 32.0 * c + 12.0 * c * (p.nsets - 1);
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = p; }
   }
   return best;

@@ -248,6 +248,7 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
     CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32));
     attr_set = true;
   }
+  CTG_CUDA(ctx, cudaStreamSynchronize(st));  // other streams (prover lanes) may use the tables next
   ctx->domains[log_n] = d;
   *out = &ctx->domains[log_n];
   return CTG_OK;

@@ -20,6 +20,11 @@
 struct ctg_pk {
   uint64_t m, ni, nw, n;
   int log_n;
+  // point-range shard (multi-GPU): this key holds positions [lo, lo + cnt) of each extended query
+  int shard_index = 0, shard_count = 1;
+  uint64_t ext_lo = 0, ext_cnt = 0;  // of a_ext / b1_ext / b2_ext (m + 3 positions)
+  uint64_t l_lo = 0, l_cnt = 0;      // of l (num_witness positions)
+  uint64_t h_lo = 0, h_cnt = 0;      // of h_ext (n positions, bit-reversed order)
   ctg::Bases a_ext, b1_ext, b2_ext, l, h_ext;
 };
 struct ctg_r1cs {
@@ -70,15 +75,31 @@ __global__ void bitrev_gather_fr_kernel(const Fr* __restrict__ in, Fr* __restric
   uint64_t j = log_n == 0 ? 0 : (uint64_t)(__brev((uint32_t)i) >> (32 - log_n));
   out[i] = in[j];
 }
-// dst[bitrev(i)] = src[i] for i < count  (count = n - 1), 96-byte points
-__global__ void bitrev_scatter_g1_kernel(const G1Affine* __restrict__ src, G1Affine* __restrict__ dst, uint64_t count, int log_n) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// dst[j - lo] = src[bitrev(j)] for j in [lo, lo + cnt) with bitrev(j) < count (count = n - 1), 96-byte points
+__global__ void bitrev_gather_g1_kernel(const G1Affine* __restrict__ src, G1Affine* __restrict__ dst, uint64_t count, int log_n, uint64_t lo, uint64_t cnt) {
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= cnt) return;
+  const uint64_t j = lo + t;
+  const uint64_t i = log_n == 0 ? 0 : (uint64_t)(__brev((uint32_t)j) >> (32 - log_n));
   if (i >= count) return;
-  uint64_t j = log_n == 0 ? 0 : (uint64_t)(__brev((uint32_t)i) >> (32 - log_n));
   const uint4* s = reinterpret_cast<const uint4*>(src + i);
-  uint4* d = reinterpret_cast<uint4*>(dst + j);
+  uint4* d = reinterpret_cast<uint4*>(dst + t);
 #pragma unroll
   for (int k = 0; k < 6; k++) d[k] = s[k];
+}
+// sums the per-rank partial results of a sharded proof: in[k][0..3] G1 (A, B1, L, H), in2[k] G2
+__global__ void __launch_bounds__(160) combine_partials_kernel(const G1XYZZ* g1, const G2XYZZ* g2, uint32_t k, G1XYZZ* out_g1, G2XYZZ* out_g2) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane != 0) return;
+  if (warp < 4) {
+    G1XYZZ acc = g1[warp];
+    for (uint32_t i = 1; i < k; i++) acc = xyzz_add(acc, g1[(size_t)i * 4 + warp]);
+    out_g1[warp] = acc;
+  } else {
+    G2XYZZ acc = g2[0];
+    for (uint32_t i = 1; i < k; i++) acc = xyzz_add(acc, g2[i]);
+    *out_g2 = acc;
+  }
 }
 
 // ---- final assembly ---------------------------------------------------------------------------
@@ -114,7 +135,7 @@ __global__ void __launch_bounds__(96) finalize_kernel(FinalizeIn in, ctg_proof* 
   }
 }
 
-// ---- host -----------------------------------------------------------------------------------
+// ---- host: key and R1CS residency -------------------------------------------------------------
 static void free_bases(Bases& b) { if (b.pts) cudaFree(b.pts); b.pts = nullptr; }
 
 template <class A>
@@ -131,8 +152,34 @@ static int32_t make_bases(ctg_ctx* ctx, Bases& out, int group, uint64_t n, int c
 }
 static int32_t finish_bases(ctg_ctx* ctx, Bases& b) { return b.group == 1 ? g1_precompute(ctx, b, ctx->stream) : g2_precompute(ctx, b, ctx->stream); }
 
-int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, ctg_pk** out) {
+// positions [lo, lo + cnt) of (query ++ extras[0..3)) -> dst; extras may hold nullptr (= point at infinity, dst is pre-zeroed)
+template <class A>
+static cudaError_t upload_ext_range(A* dst, const A* query, uint64_t m, const A* const extras[3], uint64_t lo, uint64_t cnt, cudaStream_t st) {
+  const uint64_t hi = lo + cnt;
+  if (lo < m) {
+    const uint64_t q_hi = hi < m ? hi : m;
+    cudaError_t e = cudaMemcpyAsync(dst, query + lo, (q_hi - lo) * sizeof(A), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+  }
+  for (int k = 0; k < 3; k++) {
+    const uint64_t pos = m + k;
+    if (pos >= lo && pos < hi && extras[k]) {
+      cudaError_t e = cudaMemcpyAsync(dst + (pos - lo), extras[k], sizeof(A), cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) return e;
+    }
+  }
+  return cudaSuccess;
+}
+
+static void shard_range(uint64_t total, int index, int count, uint64_t* lo, uint64_t* cnt) {
+  const uint64_t a = total * (uint64_t)index / (uint64_t)count, b = total * (uint64_t)(index + 1) / (uint64_t)count;
+  *lo = a;
+  *cnt = b - a;
+}
+
+int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, int shard_index, int shard_count, ctg_pk** out) {
   if (!v || !out) return fail(ctx, CTG_ERR_INVALID, "pk_upload: null argument");
+  if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(ctx, CTG_ERR_INVALID, "pk_upload: bad shard index / count");
   const uint64_t m = v->a_len;
   if (m < ni || m == 0 || v->b_g1_len != m || v->b_g2_len != m) return fail(ctx, CTG_ERR_INVALID, "pk_upload: a/b query lengths must equal num_instance + num_witness");
   const uint64_t nw = m - ni;
@@ -142,36 +189,37 @@ int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, 
   if (v->h_len + 1 != n) return fail(ctx, CTG_ERR_INVALID, "pk_upload: h_query length must be domain size - 1");
   ctg_pk* pk = new ctg_pk();
   pk->m = m; pk->ni = ni; pk->nw = nw; pk->n = n; pk->log_n = log_n;
+  pk->shard_index = shard_index; pk->shard_count = shard_count;
+  shard_range(m + 3, shard_index, shard_count, &pk->ext_lo, &pk->ext_cnt);
+  shard_range(nw, shard_index, shard_count, &pk->l_lo, &pk->l_cnt);
+  shard_range(n, shard_index, shard_count, &pk->h_lo, &pk->h_cnt);
   cudaStream_t st = ctx->stream;
   auto cleanup = [&](int32_t rc) { free_bases(pk->a_ext); free_bases(pk->b1_ext); free_bases(pk->b2_ext); free_bases(pk->l); free_bases(pk->h_ext); delete pk; return rc; };
   memset(&pk->a_ext, 0, sizeof(Bases)); memset(&pk->b1_ext, 0, sizeof(Bases)); memset(&pk->b2_ext, 0, sizeof(Bases));
   memset(&pk->l, 0, sizeof(Bases)); memset(&pk->h_ext, 0, sizeof(Bases));
   int32_t rc;
-  if ((rc = make_bases<G1Affine>(ctx, pk->a_ext, 1, m + 3, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G1Affine>(ctx, pk->b1_ext, 1, m + 3, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G2Affine>(ctx, pk->b2_ext, 2, m + 3, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G1Affine>(ctx, pk->l, 1, nw, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G1Affine>(ctx, pk->h_ext, 1, n, copies, c_bits)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->a_ext, 1, pk->ext_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->b1_ext, 1, pk->ext_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G2Affine>(ctx, pk->b2_ext, 2, pk->ext_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->l, 1, pk->l_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->h_ext, 1, pk->h_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
 #define PK_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { ctx->last_error = std::string(#call) + ": " + cudaGetErrorString(e__); return cleanup(CTG_ERR_CUDA); } } while (0)
-  G1Affine* a = (G1Affine*)pk->a_ext.pts; G1Affine* b1 = (G1Affine*)pk->b1_ext.pts; G2Affine* b2 = (G2Affine*)pk->b2_ext.pts;
-  PK_CUDA(cudaMemcpyAsync(a, v->a_query, m * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(a + m, v->alpha_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(a + m + 1, v->delta_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(b1, v->b_g1_query, m * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(b1 + m, v->beta_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(b1 + m + 2, v->delta_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(b2, v->b_g2_query, m * sizeof(G2Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(b2 + m, v->beta_g2, sizeof(G2Affine), cudaMemcpyHostToDevice, st));
-  PK_CUDA(cudaMemcpyAsync(b2 + m + 2, v->delta_g2, sizeof(G2Affine), cudaMemcpyHostToDevice, st));
-  if (nw) PK_CUDA(cudaMemcpyAsync(pk->l.pts, v->l_query, nw * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-  // h_query: stage natural order in scratch, scatter to bit-reversed slots
-  if (n > 1) {
+  const G1Affine* a_extra[3] = {(const G1Affine*)v->alpha_g1, (const G1Affine*)v->delta_g1, nullptr};
+  const G1Affine* b1_extra[3] = {(const G1Affine*)v->beta_g1, nullptr, (const G1Affine*)v->delta_g1};
+  const G2Affine* b2_extra[3] = {(const G2Affine*)v->beta_g2, nullptr, (const G2Affine*)v->delta_g2};
+  PK_CUDA(upload_ext_range((G1Affine*)pk->a_ext.pts, (const G1Affine*)v->a_query, m, a_extra, pk->ext_lo, pk->ext_cnt, st));
+  PK_CUDA(upload_ext_range((G1Affine*)pk->b1_ext.pts, (const G1Affine*)v->b_g1_query, m, b1_extra, pk->ext_lo, pk->ext_cnt, st));
+  PK_CUDA(upload_ext_range((G2Affine*)pk->b2_ext.pts, (const G2Affine*)v->b_g2_query, m, b2_extra, pk->ext_lo, pk->ext_cnt, st));
+  if (pk->l_cnt) PK_CUDA(cudaMemcpyAsync(pk->l.pts, (const G1Affine*)v->l_query + pk->l_lo, pk->l_cnt * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+  // h_query: stage natural order in scratch, gather this shard's bit-reversed positions; position n-1 holds delta_g1
+  if (n > 1 && pk->h_cnt) {
     if ((rc = ensure_scratch(ctx, (n - 1) * sizeof(G1Affine))) != CTG_OK) return cleanup(rc);
     PK_CUDA(cudaMemcpyAsync(ctx->scratch, v->h_query, (n - 1) * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
-    bitrev_scatter_g1_kernel<<<(unsigned)((n - 1 + 255) / 256), 256, 0, st>>>((const G1Affine*)ctx->scratch, (G1Affine*)pk->h_ext.pts, n - 1, log_n);
+    bitrev_gather_g1_kernel<<<(unsigned)((pk->h_cnt + 255) / 256), 256, 0, st>>>((const G1Affine*)ctx->scratch, (G1Affine*)pk->h_ext.pts, n - 1, log_n, pk->h_lo, pk->h_cnt);
     ctx->launches++;
   }
-  PK_CUDA(cudaMemcpyAsync((G1Affine*)pk->h_ext.pts + (n - 1), v->delta_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+  if (n - 1 >= pk->h_lo && n - 1 < pk->h_lo + pk->h_cnt)
+    PK_CUDA(cudaMemcpyAsync((G1Affine*)pk->h_ext.pts + (n - 1 - pk->h_lo), v->delta_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
   for (Bases* b : {&pk->a_ext, &pk->b1_ext, &pk->b2_ext, &pk->l, &pk->h_ext})
     if ((rc = finish_bases(ctx, *b)) != CTG_OK) return cleanup(rc);
   PK_CUDA(cudaStreamSynchronize(st));
@@ -225,6 +273,7 @@ void r1cs_free(ctg_r1cs* r) {
   delete r;
 }
 
+// ---- host: witness map ------------------------------------------------------------------------
 // d_z: m (+3) Montgomery elements on the device.  d_abc: 3 * n scratch.  Leaves h (bit-reversed,
 // Montgomery) in d_abc[0..n).
 static int32_t witness_map_dev(ctg_ctx* ctx, const ctg_r1cs* r, const Fr* d_z, Fr* d_abc, cudaStream_t st) {
@@ -259,70 +308,215 @@ int32_t witness_map_host(ctg_ctx* ctx, const ctg_r1cs* r, const ctg_fr* z, ctg_f
   return CTG_OK;
 }
 
-int32_t prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out, ctg_timings* tm) {
-  if (!pk || !r || !z || !rr || !ss || !out) return fail(ctx, CTG_ERR_INVALID, "prove: null argument");
-  if (pk->ni != r->ni || pk->nw != r->nw || pk->n != r->n) return fail(ctx, CTG_ERR_INVALID, "prove: proving key and R1CS shapes differ");
+// ---- host: prover lanes -----------------------------------------------------------------------
+static int32_t lane_init(ctg_ctx* ctx, int idx) {
+  ProveLane& L = ctx->lanes[idx];
+  if (L.ready) { if (idx == 0) L.st[0] = ctx->stream; return CTG_OK; }
+  for (int i = 0; i < 5; i++) {
+    if (idx == 0 && i == 0) { L.st[0] = ctx->stream; continue; }
+    CTG_CUDA(ctx, cudaStreamCreateWithFlags(&L.st[i], cudaStreamNonBlocking));
+  }
+  CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_z, cudaEventDisableTiming));
+  for (auto& e : L.ev_done) CTG_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (auto& e : L.ev_t) CTG_CUDA(ctx, cudaEventCreate(&e));
+  L.ready = true;
+  return CTG_OK;
+}
+void lanes_destroy(ctg_ctx* ctx) {
+  for (int idx = 0; idx < kMaxLanes; idx++) {
+    ProveLane& L = ctx->lanes[idx];
+    if (!L.ready) continue;
+    for (int i = 0; i < 5; i++) {
+      if (L.st[i]) cudaStreamSynchronize(L.st[i]);
+      if (!(idx == 0 && i == 0) && L.st[i]) cudaStreamDestroy(L.st[i]);
+      msm_ws_free(L.ws[i]);
+    }
+    if (L.scratch) cudaFree(L.scratch);
+    cudaEventDestroy(L.ev_z);
+    for (auto& e : L.ev_done) cudaEventDestroy(e);
+    for (auto& e : L.ev_t) cudaEventDestroy(e);
+    L = ProveLane();
+  }
+  if (ctx->pinned_proofs) cudaFreeHost(ctx->pinned_proofs);
+  ctx->pinned_proofs = nullptr;
+}
+static int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
+  if (bytes <= L.scratch_bytes) return CTG_OK;
+  if (L.scratch) {
+    for (int i = 0; i < 5; i++) CTG_CUDA(ctx, cudaStreamSynchronize(L.st[i]));
+    cudaFree(L.scratch);
+    L.scratch = nullptr; L.scratch_bytes = 0;
+  }
+  const size_t want = bytes + bytes / 8 + 4096;
+  if (cudaMalloc(&L.scratch, want) != cudaSuccess) { cudaGetLastError(); return fail(ctx, CTG_ERR_OOM, "out of device memory for prover scratch"); }
+  L.scratch_bytes = want;
+  return CTG_OK;
+}
+
+// Enqueues one proof (or one shard's partial sums) on a lane; no host synchronisation.
+//   d_proof_out != nullptr : full proof (shard_count must be 1), written to device memory d_proof_out
+//   d_partials_out != nullptr : this shard's partial sums [A, B1, L, H] (4 G1 XYZZ) then B2 (G2 XYZZ), 1152 bytes
+static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const Fr& r_m, const Fr& s_m,
+                             ctg_proof* host_proof_out, void* host_partials_out, bool timed) {
+  CTG_TRY(lane_init(ctx, lane_idx));
+  ProveLane& L = ctx->lanes[lane_idx];
   const uint64_t n = r->n, m = pk->m;
-  cudaStream_t st = ctx->stream;
   // scratch: z_ext (m+3) | a,b,c (3n) | results: 4 G1 XYZZ + 1 G2 XYZZ | proof
   const size_t fr_elems = m + 3 + 3 * n;
   const size_t bytes = fr_elems * sizeof(Fr) + 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ) + sizeof(ctg_proof) + 256;
-  CTG_TRY(ensure_scratch(ctx, bytes));
-  Fr* d_z = (Fr*)ctx->scratch;
+  CTG_TRY(lane_scratch(ctx, L, bytes));
+  Fr* d_z = (Fr*)L.scratch;
   Fr* d_abc = d_z + (m + 3);
   char* tail = (char*)(d_abc + 3 * n);
   tail = (char*)(((uintptr_t)tail + 63) & ~(uintptr_t)63);
   G1XYZZ* d_g1 = (G1XYZZ*)tail;           // [0]=A [1]=B1 [2]=L [3]=H
   G2XYZZ* d_g2 = (G2XYZZ*)(d_g1 + 4);
   ctg_proof* d_proof = (ctg_proof*)(d_g2 + 1);
-  Fr r_m, s_m;
-  memcpy(&r_m, rr, sizeof(Fr));
-  memcpy(&s_m, ss, sizeof(Fr));
-  const bool timed = tm != nullptr;
-  if (!ctx->events_ready) {
-    for (auto& e : ctx->ev) CTG_CUDA(ctx, cudaEventCreate(&e));
-    ctx->events_ready = true;
-  }
-  cudaEvent_t* ev = ctx->ev + 4;  // ev[0..3] belong to the MSM stage timers
+  cudaStream_t s0 = L.st[0];
   int ne = 0;
-  auto mark = [&]() { if (timed && ne < 10) cudaEventRecord(ev[ne++], st); };
-  mark();
-  CTG_CUDA(ctx, cudaMemcpyAsync(d_z, z, m * sizeof(Fr), cudaMemcpyHostToDevice, st));
-  set_tail_kernel<<<1, 32, 0, st>>>(d_z, m, r_m, s_m);
+  auto mark = [&](cudaStream_t st) { if (timed && ne < 16) cudaEventRecord(L.ev_t[ne], st); ne++; };
+  mark(s0);                                                                   // 0
+  CTG_CUDA(ctx, cudaMemcpyAsync(d_z, z, m * sizeof(Fr), cudaMemcpyHostToDevice, s0));
+  set_tail_kernel<<<1, 32, 0, s0>>>(d_z, m, r_m, s_m);
   CTG_KERNEL_CHECK(ctx);
-  mark();
-  CTG_TRY(witness_map_dev(ctx, r, d_z, d_abc, st));
-  set_h_tail_kernel<<<1, 32, 0, st>>>(d_abc, n, r_m, s_m);
-  CTG_KERNEL_CHECK(ctx);
-  mark();
-  MsmWorkspace& ws = ctx->ws[0];
-  CTG_TRY(msm_g1_run(ctx, ws, pk->h_ext, (const uint32_t*)d_abc, n, true, d_g1 + 3, st, nullptr));
-  mark();
-  CTG_TRY(msm_g1_run(ctx, ws, pk->l, (const uint32_t*)(d_z + pk->ni), pk->nw, true, d_g1 + 2, st, nullptr));
-  mark();
-  CTG_TRY(msm_g1_run(ctx, ws, pk->a_ext, (const uint32_t*)d_z, m + 3, true, d_g1 + 0, st, nullptr));
-  mark();
-  CTG_TRY(msm_g1_run(ctx, ws, pk->b1_ext, (const uint32_t*)d_z, m + 3, true, d_g1 + 1, st, nullptr));
-  mark();
-  CTG_TRY(msm_g2_run(ctx, ws, pk->b2_ext, (const uint32_t*)d_z, m + 3, true, d_g2, st, nullptr));
-  mark();
-  FinalizeIn fin{d_g1 + 0, d_g1 + 1, d_g1 + 2, d_g1 + 3, d_g2, r_m, s_m};
-  finalize_kernel<<<1, 96, 0, st>>>(fin, d_proof);
-  CTG_KERNEL_CHECK(ctx);
-  CTG_CUDA(ctx, cudaMemcpyAsync(out, d_proof, sizeof(ctg_proof), cudaMemcpyDeviceToHost, st));
-  mark();
-  CTG_CUDA(ctx, cudaStreamSynchronize(st));
-  if (timed) {
-    memset(tm, 0, sizeof(*tm));
-    float* dst[8] = {&tm->h2d_ms, &tm->witness_map_ms, &tm->msm_h_ms, &tm->msm_l_ms, &tm->msm_a_ms, &tm->msm_b_g1_ms, &tm->msm_b_g2_ms, &tm->finalize_ms};
-    for (int i = 0; i + 1 < ne && i < 8; i++) cudaEventElapsedTime(dst[i], ev[i], ev[i + 1]);
-    cudaEventElapsedTime(&tm->total_ms, ev[0], ev[ne - 1]);
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_z, s0));
+  mark(s0);                                                                   // 1
+  // assignment-only MSMs on their own streams
+  struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
+  const Job jobs[4] = {{1, &pk->l, d_z + pk->ni + pk->l_lo, pk->l_cnt, 2},
+                       {2, &pk->a_ext, d_z + pk->ext_lo, pk->ext_cnt, 0},
+                       {3, &pk->b1_ext, d_z + pk->ext_lo, pk->ext_cnt, 1},
+                       {4, &pk->b2_ext, d_z + pk->ext_lo, pk->ext_cnt, -1}};
+  for (const Job& j : jobs) {
+    cudaStream_t st = L.st[j.stream];
+    CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
+    mark(st);                                                                 // 2,4,6,8
+    if (j.g1_slot >= 0) CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr));
+    else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
+    mark(st);                                                                 // 3,5,7,9
+    CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
   }
+  // witness map and the H MSM on the lane's main stream
+  CTG_TRY(witness_map_dev(ctx, r, d_z, d_abc, s0));
+  set_h_tail_kernel<<<1, 32, 0, s0>>>(d_abc, n, r_m, s_m);
+  CTG_KERNEL_CHECK(ctx);
+  mark(s0);                                                                   // 10
+  CTG_TRY(msm_g1_run(ctx, L.ws[0], pk->h_ext, (const uint32_t*)(d_abc + pk->h_lo), pk->h_cnt, true, d_g1 + 3, s0, nullptr));
+  mark(s0);                                                                   // 11
+  for (int i = 1; i < 5; i++) CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_done[i], 0));
+  if (host_partials_out) {
+    CTG_CUDA(ctx, cudaMemcpyAsync(host_partials_out, d_g1, 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ), cudaMemcpyDeviceToHost, s0));
+  } else {
+    FinalizeIn fin{d_g1 + 0, d_g1 + 1, d_g1 + 2, d_g1 + 3, d_g2, r_m, s_m};
+    finalize_kernel<<<1, 96, 0, s0>>>(fin, d_proof);
+    CTG_KERNEL_CHECK(ctx);
+    CTG_CUDA(ctx, cudaMemcpyAsync(host_proof_out, d_proof, sizeof(ctg_proof), cudaMemcpyDeviceToHost, s0));
+  }
+  mark(s0);                                                                   // 12
   return CTG_OK;
 }
 
-}  // namespace ctg
+static void lane_timings(ProveLane& L, ctg_timings* tm) {
+  memset(tm, 0, sizeof(*tm));
+  auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, L.ev_t[a], L.ev_t[b]); return ms; };
+  tm->h2d_ms = el(0, 1);
+  tm->msm_l_ms = el(2, 3); tm->msm_a_ms = el(4, 5); tm->msm_b_g1_ms = el(6, 7); tm->msm_b_g2_ms = el(8, 9);
+  tm->witness_map_ms = el(1, 10);
+  tm->msm_h_ms = el(10, 11);
+  tm->finalize_ms = el(11, 12);   // includes waiting for the other streams
+  tm->total_ms = el(0, 12);
+}
 
-namespace ctg {
+static int32_t check_prove_args(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r) {
+  if (pk->ni != r->ni || pk->nw != r->nw || pk->n != r->n) return fail(ctx, CTG_ERR_INVALID, "prove: proving key and R1CS shapes differ");
+  return CTG_OK;
+}
+
+int32_t prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out, ctg_timings* tm) {
+  if (!pk || !r || !z || !rr || !ss || !out) return fail(ctx, CTG_ERR_INVALID, "prove: null argument");
+  CTG_TRY(check_prove_args(ctx, pk, r));
+  if (pk->shard_count != 1) return fail(ctx, CTG_ERR_STATE, "prove: the key is a shard; use ctg_prove_partial + ctg_prove_combine");
+  Fr r_m, s_m;
+  memcpy(&r_m, rr, sizeof(Fr));
+  memcpy(&s_m, ss, sizeof(Fr));
+  CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, out, nullptr, tm != nullptr));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));
+  if (tm) lane_timings(ctx->lanes[0], tm);
+  return CTG_OK;
+}
+
+// Independent proofs pipelined over the lanes: while one proof sits in its latency-bound tails (bucket reduction,
+// inversions) the next one's kernels fill the SMs.  Results are staged in pinned memory.
+int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch, ctg_proof* out) {
+  CTG_TRY(check_prove_args(ctx, pk, r));
+  if (pk->shard_count != 1) return fail(ctx, CTG_ERR_STATE, "prove_batch: the key is a shard");
+  if (n_proofs == 0) return CTG_OK;
+  const size_t need = (size_t)n_proofs * sizeof(ctg_proof);
+  if (need > ctx->pinned_proofs_bytes) {
+    if (ctx->pinned_proofs) cudaFreeHost(ctx->pinned_proofs);
+    ctx->pinned_proofs = nullptr; ctx->pinned_proofs_bytes = 0;
+    CTG_CUDA(ctx, cudaMallocHost(&ctx->pinned_proofs, need));
+    ctx->pinned_proofs_bytes = need;
+  }
+  ctg_proof* staged = (ctg_proof*)ctx->pinned_proofs;
+  // small circuits are latency-bound: use every lane; large ones saturate the GPU alone and only need two
+  const int lanes = r->n <= (1u << 18) ? kMaxLanes : 2;
+  const uint64_t m = pk->m;
+  for (uint32_t i = 0; i < n_proofs; i++) {
+    Fr r_m, s_m;
+    memcpy(&r_m, rs_batch + 2 * (size_t)i, sizeof(Fr));
+    memcpy(&s_m, rs_batch + 2 * (size_t)i + 1, sizeof(Fr));
+    CTG_TRY(prove_enqueue(ctx, (int)(i % lanes), pk, r, z_batch + (size_t)i * m, r_m, s_m, staged + i, nullptr, false));
+  }
+  for (int l = 0; l < lanes; l++)
+    if (ctx->lanes[l].ready) CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[l].st[0]));
+  memcpy(out, staged, need);
+  return CTG_OK;
+}
+
+// One shard's partial sums (multi-GPU prove): out = [A, B1, L, H] as G1 XYZZ then B2 as G2 XYZZ (1152 bytes, host)
+int32_t prove_partial(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, void* out_partials, ctg_timings* tm) {
+  if (!pk || !r || !z || !rr || !ss || !out_partials) return fail(ctx, CTG_ERR_INVALID, "prove_partial: null argument");
+  CTG_TRY(check_prove_args(ctx, pk, r));
+  Fr r_m, s_m;
+  memcpy(&r_m, rr, sizeof(Fr));
+  memcpy(&s_m, ss, sizeof(Fr));
+  CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, nullptr, out_partials, tm != nullptr));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));
+  if (tm) lane_timings(ctx->lanes[0], tm);
+  return CTG_OK;
+}
+
+// Sum of k shards' partials, then the usual assembly: C = s*A + r*B1 + L + H', affine (A, B2, C)
+int32_t prove_combine(ctg_ctx* ctx, const void* host_partials, uint32_t k, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out) {
+  if (!host_partials || !rr || !ss || !out || k == 0) return fail(ctx, CTG_ERR_INVALID, "prove_combine: bad argument");
+  const size_t one = 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ);
+  CTG_TRY(ensure_scratch(ctx, (size_t)(k + 1) * one + sizeof(ctg_proof) + 256));
+  cudaStream_t st = ctx->stream;
+  // device layout: g1[k][4] | g2[k] | sums: g1[4], g2 | proof
+  G1XYZZ* d_g1 = (G1XYZZ*)ctx->scratch;
+  G2XYZZ* d_g2 = (G2XYZZ*)(d_g1 + (size_t)4 * k);
+  G1XYZZ* d_s1 = (G1XYZZ*)(d_g2 + k);
+  G2XYZZ* d_s2 = (G2XYZZ*)(d_s1 + 4);
+  ctg_proof* d_proof = (ctg_proof*)(d_s2 + 1);
+  for (uint32_t i = 0; i < k; i++) {
+    const char* src = (const char*)host_partials + (size_t)i * one;
+    CTG_CUDA(ctx, cudaMemcpyAsync(d_g1 + (size_t)4 * i, src, 4 * sizeof(G1XYZZ), cudaMemcpyHostToDevice, st));
+    CTG_CUDA(ctx, cudaMemcpyAsync(d_g2 + i, src + 4 * sizeof(G1XYZZ), sizeof(G2XYZZ), cudaMemcpyHostToDevice, st));
+  }
+  combine_partials_kernel<<<1, 160, 0, st>>>(d_g1, d_g2, k, d_s1, d_s2);
+  CTG_KERNEL_CHECK(ctx);
+  Fr r_m, s_m;
+  memcpy(&r_m, rr, sizeof(Fr));
+  memcpy(&s_m, ss, sizeof(Fr));
+  FinalizeIn fin{d_s1 + 0, d_s1 + 1, d_s1 + 2, d_s1 + 3, d_s2, r_m, s_m};
+  finalize_kernel<<<1, 96, 0, st>>>(fin, d_proof);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_CUDA(ctx, cudaMemcpyAsync(out, d_proof, sizeof(ctg_proof), cudaMemcpyDeviceToHost, st));
+  CTG_CUDA(ctx, cudaStreamSynchronize(st));
+  return CTG_OK;
+}
+
 uint64_t pk_num_vars(const ctg_pk* pk) { return pk->m; }
+
 }  // namespace ctg

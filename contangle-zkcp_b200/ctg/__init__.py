@@ -18,6 +18,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "libctg_groth16.so")
 
 FR_W, FQ_W, G1_W, G2_W = 8, 12, 24, 48
+PARTIAL_W = 4 * 2 * G1_W + 2 * G2_W   # ctg_proof_partial: 4 G1 XYZZ + 1 G2 XYZZ = 288 words (1152 B)
 SCALARS_CANONICAL, SCALARS_MONT, MSM_TIMED = 0, 1, 0x100
 FIELD_FR, FIELD_FQ, FIELD_FQ2 = 0, 1, 2
 OP_MUL, OP_ADD, OP_SUB = 0, 1, 2
@@ -31,7 +32,8 @@ EXPORTS = [
     "ctg_bases_download", "ctg_bases_free", "ctg_bases_len", "ctg_msm_g1", "ctg_msm_g2", "ctg_msm_g1_dev",
     "ctg_msm_g2_dev", "ctg_msm_g1_partial", "ctg_msm_g2_partial", "ctg_g1_combine", "ctg_g2_combine",
     "ctg_g1_combine_dev", "ctg_g2_combine_dev", "ctg_pk_upload", "ctg_pk_free", "ctg_r1cs_upload",
-    "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch",
+    "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch", "ctg_pk_upload_shard", "ctg_prove_partial",
+    "ctg_prove_combine",
 ]
 
 
@@ -244,8 +246,9 @@ class Context:
         self._check(fn(self.h, C.c_void_p(d_partials), C.c_uint32(k), C.c_void_p(d_out_affine)))
 
     # ---- proving key / R1CS / prover
-    def upload_pk(self, pk: dict, num_instance, num_constraints, copies=0, c_bits=0):
-        """pk: dict of arrays alpha_g1, beta_g1, delta_g1, beta_g2, delta_g2, a_query, b_g1_query, b_g2_query, h_query, l_query."""
+    def upload_pk(self, pk: dict, num_instance, num_constraints, copies=0, c_bits=0, shard=None):
+        """pk: dict of arrays alpha_g1, beta_g1, delta_g1, beta_g2, delta_g2, a_query, b_g1_query, b_g2_query, h_query, l_query.
+        shard=(index, count): keep only that point range of every query (multi-GPU; use with prove_partial)."""
         v = PkView()
         keep = []
         for k, w in (("alpha_g1", G1_W), ("beta_g1", G1_W), ("delta_g1", G1_W), ("beta_g2", G2_W), ("delta_g2", G2_W)):
@@ -254,7 +257,11 @@ class Context:
             a = _arr(pk[k]).reshape(-1, w); keep.append(a); setattr(v, k, a.ctypes.data)
             setattr(v, k.replace("_query", "_len"), a.shape[0])
         h = C.c_void_p()
-        self._check(load().ctg_pk_upload(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits, C.byref(h)))
+        if shard is None:
+            self._check(load().ctg_pk_upload(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits, C.byref(h)))
+        else:
+            self._check(load().ctg_pk_upload_shard(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits,
+                                                   int(shard[0]), int(shard[1]), C.byref(h)))
         return DevicePk(self, h, pk["a_query"].shape[0])
 
     def upload_r1cs(self, r1cs: dict):
@@ -293,6 +300,36 @@ class Context:
         self._check(load().ctg_prove(self.h, pk.handle, r1cs.handle, _ptr(z), _ptr(r), _ptr(s), _ptr(out), C.byref(t) if timed else None))
         proof = (out[:G1_W].copy(), out[G1_W:G1_W + G2_W].copy(), out[G1_W + G2_W:].copy())
         return (proof, t.as_dict()) if timed else proof
+
+    def prove_batch(self, pk: "DevicePk", r1cs: "DeviceR1cs", z_batch, rs_batch):
+        """n independent proofs with one key: z_batch (n, m, 8), rs_batch (n, 2, 8).  Returns (n, 96) words: A | B | C."""
+        z_batch = _arr(z_batch, FR_W)
+        rs_batch = _arr(rs_batch, FR_W)
+        n = z_batch.shape[0]
+        if z_batch.ndim != 3 or z_batch.shape[1] != r1cs.m or rs_batch.shape != (n, 2, FR_W) or pk.m != r1cs.m:
+            raise CtgError("prove_batch: shapes must be z (n, m, 8), rs (n, 2, 8)")
+        out = np.zeros((n, G1_W + G2_W + G1_W), dtype=np.uint32)
+        self._check(load().ctg_prove_batch(self.h, pk.handle, r1cs.handle, C.c_uint32(n), _ptr(z_batch), _ptr(rs_batch), _ptr(out)))
+        return out
+
+    def prove_partial(self, pk_shard: "DevicePk", r1cs: "DeviceR1cs", z, r, s, timed=False):
+        """This GPU's share of a sharded proof: (288,) words of partial sums (ctg_proof_partial)."""
+        z = _arr(z, FR_W)
+        if z.shape[0] != r1cs.m or pk_shard.m != r1cs.m:
+            raise CtgError("prove_partial: assignment / key / R1CS sizes differ")
+        r, s = _arr(r).reshape(FR_W), _arr(s).reshape(FR_W)
+        out = np.zeros(PARTIAL_W, dtype=np.uint32)
+        t = Timings()
+        self._check(load().ctg_prove_partial(self.h, pk_shard.handle, r1cs.handle, _ptr(z), _ptr(r), _ptr(s), _ptr(out), C.byref(t) if timed else None))
+        return (out, t.as_dict()) if timed else out
+
+    def prove_combine(self, partials, r, s):
+        """Sum the shards' partials (k, 288) and assemble the proof (A, B, C)."""
+        partials = _arr(partials, PARTIAL_W).reshape(-1, PARTIAL_W)
+        r, s = _arr(r).reshape(FR_W), _arr(s).reshape(FR_W)
+        out = np.zeros(G1_W + G2_W + G1_W, dtype=np.uint32)
+        self._check(load().ctg_prove_combine(self.h, _ptr(partials), C.c_uint32(partials.shape[0]), _ptr(r), _ptr(s), _ptr(out)))
+        return out[:G1_W].copy(), out[G1_W:G1_W + G2_W].copy(), out[G1_W + G2_W:].copy()
 
     def prove_ptr(self, pk, r1cs, z_ptr, r, s, out):
         """Same with a raw host pointer for z (e.g. a pinned torch tensor) and a preallocated output (96 words)."""

@@ -1,0 +1,52 @@
+"""Multi-GPU plumbing for the sharded prover: one process per GPU, each holding a point-range shard of
+the proving key (ctg_pk_upload_shard); a proof is `ctg_prove_partial` on every rank, one all_gather of 1152 bytes per
+rank over NCCL (NVLink / NVSwitch), and `ctg_prove_combine` on rank 0.  The same code runs over gloo with CPU tensors
+(tests/test_sharding_cpu.py exercises the rank arithmetic and the exchange without a GPU).
+
+torch.distributed is plumbing here, nothing else: the payload is a byte tensor.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import PARTIAL_W
+
+
+def shard_range(total: int, index: int, count: int):
+    """[lo, lo + cnt) of `total` positions owned by shard `index` of `count` (same arithmetic as csrc/prove.cu)."""
+    if count < 1 or not 0 <= index < count:
+        raise ValueError("bad shard index / count")
+    lo = total * index // count
+    hi = total * (index + 1) // count
+    return lo, hi - lo
+
+
+def key_shard_ranges(num_instance: int, num_witness: int, domain_size: int, index: int, count: int):
+    """Ranges a shard keeps of each extended query: ext = a/b1/b2 query ++ 3 fixed points, l, h (bit-reversed order)."""
+    m = num_instance + num_witness
+    return {"ext": shard_range(m + 3, index, count), "l": shard_range(num_witness, index, count),
+            "h": shard_range(domain_size, index, count)}
+
+
+def all_gather_partials(partial: np.ndarray, dist, device=None):
+    """All-gather one (PARTIAL_W,) uint32 partial per rank -> (world, PARTIAL_W), ordered by rank.
+    `dist` is torch.distributed (initialised); `device` = the rank's CUDA device for NCCL, None for gloo/CPU."""
+    import torch
+    partial = np.ascontiguousarray(partial, dtype=np.uint32).reshape(PARTIAL_W)
+    t = torch.from_numpy(partial.view(np.int32).copy())
+    if device is not None:
+        t = t.to(device)
+    world = dist.get_world_size()
+    out = torch.empty(world * PARTIAL_W, dtype=torch.int32, device=t.device)   # flat: gloo and NCCL both accept it
+    dist.all_gather_into_tensor(out, t)
+    return out.cpu().numpy().view(np.uint32).reshape(world, PARTIAL_W)
+
+
+def sharded_prove(ctx, pk_shard, r1cs, z, r, s, dist, device=None):
+    """ark_groth16::create_proof over `world` GPUs.  Every rank calls this with its own context and key shard and the
+    same (z, r, s); rank 0 returns (A, B, C), the other ranks return None."""
+    part = ctx.prove_partial(pk_shard, r1cs, z, r, s)
+    allp = all_gather_partials(part, dist, device)
+    if dist.get_rank() == 0:
+        return ctx.prove_combine(allp, r, s)
+    return None

@@ -61,6 +61,9 @@ typedef struct { ctg_fq c[8]; } ctg_g2_xyzz;                       /* 384 B */
 /* ark_groth16::Proof<Bls12_381> { a: G1Affine, b: G2Affine, c: G1Affine } */
 typedef struct { ctg_g1_affine a; ctg_g2_affine b; ctg_g1_affine c; } ctg_proof;
 
+/* one GPU's share of a point-range sharded proof: partial sums of the five MSMs (see ctg_prove_partial) */
+typedef struct { ctg_g1_xyzz a, b1, l, h; ctg_g2_xyzz b2; } ctg_proof_partial;               /* 1152 B */
+
 /* ark_groth16::ProvingKey<Bls12_381> as pointers + lengths. */
 typedef struct {
   const ctg_g1_affine* alpha_g1; /* vk.alpha_g1 */
@@ -165,6 +168,10 @@ int32_t ctg_g2_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, voi
 /* ---- proving key / R1CS caches and the prover ---------------------------------------- */
 /* copies / c_bits as for ctg_bases_upload_* (applied to every query). */
 int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits, ctg_pk** out);
+/* Multi-GPU: shard `shard_index` of `shard_count` keeps only its point range of every query (one process / context per
+ * GPU; host_pk is the full key on every rank).  A sharded key works with ctg_prove_partial only. */
+int32_t ctg_pk_upload_shard(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
+                            int shard_index, int shard_count, ctg_pk** out);
 void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk);
 int32_t ctg_r1cs_upload(ctg_ctx* ctx, uint64_t num_instance, uint64_t num_witness, uint64_t num_constraints, const ctg_csr* a,
                         const ctg_csr* b, const ctg_csr* c, ctg_r1cs** out);
@@ -178,9 +185,17 @@ int32_t ctg_witness_map(ctg_ctx* ctx, const ctg_r1cs* r1cs, const ctg_fr* z, ctg
  * (m elements, z[0] = 1, Montgomery), r and s drawn by the caller (Fr::rand, r first). */
 int32_t ctg_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
                   ctg_proof* out, ctg_timings* timings /* may be NULL */);
-/* n_proofs independent assignments (z_batch: n_proofs * m), rs_batch: n_proofs * 2 (r, s) */
+/* n_proofs independent assignments (z_batch: n_proofs * m), rs_batch: n_proofs * 2 (r, s); the proofs are pipelined
+ * over several stream sets so that one proof's latency-bound tails overlap the next one's kernels */
 int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, uint32_t n_proofs, const ctg_fr* z_batch,
                         const ctg_fr* rs_batch, ctg_proof* out);
+
+/* Sharded proof: every rank computes the witness map (replicated, cheap) and the five MSMs over ITS point range, giving
+ * 1152 bytes of partial sums; the partials are gathered (NCCL all_gather over NVLink) and one rank sums them and
+ * finishes the proof: C = s*A + r*B1 + L + H, affine (A, B, C).  Replaces the same create_proof call as ctg_prove. */
+int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
+                          ctg_proof_partial* out, ctg_timings* timings /* may be NULL */);
+int32_t ctg_prove_combine(ctg_ctx* ctx, const ctg_proof_partial* partials, uint32_t k, const ctg_fr* r, const ctg_fr* s, ctg_proof* out);
 
 #ifdef __cplusplus
 }

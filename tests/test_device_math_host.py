@@ -129,3 +129,30 @@ def test_signed_digits_recompose(hm, c):
         hm.hm_signed_digits(_p(ark.ints_to_words([k], 8)[0]), C.c_int(c), C.c_int(nwin), _p(dig))
         assert all(abs(int(d)) <= 1 << (c - 1) for d in dig)
         assert sum(int(d) << (c * w) for w, d in enumerate(dig)) == k
+
+
+def test_lazy_sums_of_products(hm):
+    """Fq::mul2_add / mul2_sub / Fq2::mul2_sub (one Montgomery reduction for several products) incl. extreme operands."""
+    P = B.P_MOD
+    Rinv = pow(1 << 384, -1, P)
+    edge = [0, 1, P - 1, P - 2, (P - 1) // 2, (1 << 380) % P]
+    quads = [(a, b, c, d) for a in edge for b in (0, P - 1, 1) for c in (P - 1, 0, 2) for d in (P - 1, 0, 1)]
+    quads += [tuple(rnd.randrange(P) for _ in range(4)) for _ in range(300)]
+    arr = [ark.ints_to_words([q[k] for q in quads], 12) for k in range(4)]
+    n = len(quads)
+    for name, sign in (("hm_fq_mul2_add", 1), ("hm_fq_mul2_sub", -1)):
+        out = np.zeros_like(arr[0])
+        getattr(hm, name)(*[_p(x) for x in arr], _p(out), C.c_uint64(n))
+        want = [((a * b + sign * c * d) * Rinv) % P for a, b, c, d in quads]   # Montgomery images in, Montgomery image out
+        assert ark.words_to_ints(out) == want, name
+    # Fq2: a*b - c*d with a = (a0, a1) etc.
+    m = n // 2 * 2
+    f2 = [x[:m].reshape(m // 2, 24) for x in arr]
+    out = np.zeros_like(f2[0])
+    hm.hm_fq2_mul2_sub(*[_p(np.ascontiguousarray(x)) for x in f2], _p(out), C.c_uint64(m // 2))
+    got = ark.words_to_ints(out.reshape(m, 12))
+    for i in range(m // 2):
+        (a0, b0, c0, d0), (a1, b1, c1, d1) = quads[2 * i], quads[2 * i + 1]
+        w0 = ((a0 * b0 - a1 * b1) - (c0 * d0 - c1 * d1)) * Rinv % P
+        w1 = ((a0 * b1 + a1 * b0) - (c0 * d1 + c1 * d0)) * Rinv % P
+        assert (got[2 * i], got[2 * i + 1]) == (w0, w1), i

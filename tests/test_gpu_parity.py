@@ -148,7 +148,8 @@ def test_msm_g1_adversarial(ctx, kind):
     t.free()
 
 
-@pytest.mark.parametrize("c_bits,copies", [(4, 1), (8, 1), (8, 4), (11, 2), (13, 20), (16, 1), (16, 16), (16, 3)])
+@pytest.mark.parametrize("c_bits,copies", [(2, 1), (4, 1), (8, 1), (8, 4), (11, 2), (13, 20), (16, 1), (16, 16), (16, 3), (17, 16), (18, 15), (19, 5), (20, 13),
+                                           (21, 13)])
 def test_msm_g1_window_and_precompute_choices(ctx, c_bits, copies):
     n = 5000
     pts = _g1_bases(n, 7)
@@ -285,6 +286,54 @@ def test_prove_progression_key_dlog_closed_form(ctx, log_n):
     h = ark.fr_ints_from_mont(ark.witness_map(r1cs, zm))
     assert util.proof_to_py(got) == util.dlog_expected_proof(dl, r1cs, z, h, r, s)
     dpk.free(); dr.free()
+
+
+def test_prove_batch_matches_single_proofs(ctx):
+    """ctg_prove_batch pipelines independent proofs over several stream sets; each must equal its own ctg_prove / oracle proof."""
+    r1cs, zm0, z0 = S.poe_shape(3, gates=300, bits=40)
+    pk, _ = S.progression_pk(ctx, r1cs)
+    dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"])
+    dr = ctx.upload_r1cs(r1cs)
+    nproofs = 7
+    zs, rss = [], []
+    for i in range(nproofs):
+        _, zm, _ = S.poe_shape(3, seed=1000 + i, gates=300, bits=40)     # same shape, different witness
+        zs.append(zm)
+        rss.append(np.stack([fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD))]))
+    out = ctx.prove_batch(dpk, dr, np.stack(zs), np.stack(rss))
+    for i in range(nproofs):
+        single = ctx.prove(dpk, dr, zs[i], rss[i][0], rss[i][1])
+        assert np.array_equal(out[i], np.concatenate(single)), i
+    for i in (0, nproofs - 1):
+        want = ark.create_proof(pk, r1cs, zs[i], rss[i][0], rss[i][1])
+        assert np.array_equal(out[i], np.concatenate(want)), i
+    dpk.free(); dr.free()
+
+
+@pytest.mark.parametrize("log_n,shards", [(4, 2), (9, 3), (12, 8)])
+def test_prove_sharded_partials_combine(ctx, log_n, shards):
+    """The multi-GPU path on one GPU: every shard's ctg_prove_partial, then ctg_prove_combine, equals ctg_prove."""
+    r1cs, zm, z = S.mul_chain(log_n)
+    pk, _ = S.progression_pk(ctx, r1cs)
+    r, s = fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD))
+    dr = ctx.upload_r1cs(r1cs)
+    full = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"])
+    want = ctx.prove(full, dr, zm, r, s)
+    full.free()
+    parts = []
+    for k in range(shards):
+        sh = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], shard=(k, shards))
+        with pytest.raises(ctg.CtgError):
+            ctx.prove(sh, dr, zm, r, s)          # a shard cannot produce a whole proof
+        parts.append(ctx.prove_partial(sh, dr, zm, r, s))
+        sh.free()
+    got = ctx.prove_combine(np.stack(parts), r, s)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    if log_n <= 9:
+        for g, w in zip(got, ark.create_proof(pk, r1cs, zm, r, s)):
+            assert np.array_equal(g, w)
+    dr.free()
 
 
 def test_prove_rejects_mismatched_shapes(ctx):
