@@ -29,6 +29,7 @@ for p in (ROOT, os.path.join(ROOT, "contangle-zkcp_b200")):
 import numpy as np  # noqa: E402
 
 MAC32_PER_G1_POINT = 48_000      # 16 signed windows x (8M + 2S) x 300 MAC32 per Fq product
+MAC32_PER_MADD_EXECUTED = 2_844  # what the kernel executes per mixed addition: 8 products x 300 + one 2-product lazy reduction (444)
 METRIC = "g1_msm_throughput"
 UNIT = "Mpts/s"
 
@@ -79,6 +80,18 @@ class ClockSampler(threading.Thread):
         reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
         mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+
+
+def ncu_traffic(key):
+    """DRAM bytes (read + write) of one launch of the dominant kernel, from the committed ncu --set full capture."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[key]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+def plan_windows(ctx, bases):
+    return bases.plan()["windows"]
 
 
 def cpu_msm_sample(bases_host, scalars_host, steps=1):
@@ -235,13 +248,14 @@ def main():
         "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32 limbs (381-bit Fq, 255-bit Fr)", "data": "synthetic",
         "config": {"workload": workload_name(args.log_n, world), "points_per_gpu": n, "l2": "inputs (128 MiB scalars + 384 MiB bases per copy) exceed the 126 MB L2",
-                   "window_bits": None, "precomputed_copies": args.copies, "seed": seed},
+                   "plan": bases.plan(), "seed": seed},
         "e2e": {"value": world * n / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": 96 if world == 1 else 192,
                 "ms_per_step": ms_e2e, "ms_per_step_device_events": ms_e2e_dev},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "imad", "kernel": "msm_accumulate_kernel<Fq>", "achieved": achieved / 1e12, "peak": mac_peak / 1e12, "unit": "TMAC32/s",
-                     "frac": achieved / mac_peak, "traffic": None, "kernel_ms": acc, "step_share": acc / ms_dev,
+                     "frac": achieved / mac_peak, "traffic": ncu_traffic("msm_accumulate_g1_2^%d" % args.log_n), "kernel_ms": acc,
+                     "frac_executed": n * plan_windows(ctx, bases) * MAC32_PER_MADD_EXECUTED / (acc * 1e-3) / mac_peak, "step_share": acc / ms_dev,
                      "peak_source": "measured live: ctg_imad_peak_probe IMAD issue rate / 2 (32x32->64 MAC = 2 IMAD slots)",
                      "imad_per_s": imad_per_s, "fq_mul_per_s": fq_mul_per_s, "algorithmic_mac32_per_point": MAC32_PER_G1_POINT},
         "stages_ms": {"sort": sum(sort_ms) / len(sort_ms), "accumulate": acc, "reduce": sum(red_ms) / len(red_ms)},
@@ -299,6 +313,7 @@ def extras(ctx, torch, dev, stream, S, args):
         ntt[f"2^{lg}"] = {"ms": ms, "algorithmic_GBps": gbs, "frac_of_hbm_peak": (gbs / hbm) if hbm else None,
                           "TMAC32_per_s": macs / (ms * 1e-3) / 1e12, "frac_of_mac32_peak": macs / (ms * 1e-3) / mac_peak}
         del x
+    out["ntt_fr_forward"] = ntt
     out["ntt_note"] = ("radix-2 NTT over a 255-bit field is integer-bound on B200: 68*log2(n) MAC32 per element against 64 B of "
                        "compulsory traffic; frac_of_mac32_peak is the binding roofline, frac_of_hbm_peak the one the north star names")
     msm = {}

@@ -281,6 +281,12 @@ void ctg_bases_free(ctg_ctx* ctx, ctg_bases* bases) {
   delete bases;
 }
 uint64_t ctg_bases_len(const ctg_bases* bases) { return bases ? bases->b.n : 0; }
+int32_t ctg_bases_plan(const ctg_bases* bases, ctg_msm_plan* out) {
+  if (!bases || !out) return CTG_ERR_INVALID;
+  const MsmPlan& p = bases->b.plan;
+  out->window_bits = p.c; out->windows = p.nwin; out->copies = p.copies; out->bucket_sets = p.nsets; out->buckets_per_set = p.nbuckets_per_set;
+  return CTG_OK;
+}
 
 // ---- MSM --------------------------------------------------------------------------------------
 int32_t ctg_msm_g1_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {

@@ -29,7 +29,7 @@ EXPORTS = [
     "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch",
     "ctg_fr_mul_batch", "ctg_fq_mul_batch", "ctg_imad_peak_probe", "ctg_ntt_fr", "ctg_ntt_fr_dev",
     "ctg_bases_upload_g1", "ctg_bases_upload_g2", "ctg_bases_progression_g1", "ctg_bases_progression_g2",
-    "ctg_bases_download", "ctg_bases_free", "ctg_bases_len", "ctg_msm_g1", "ctg_msm_g2", "ctg_msm_g1_dev",
+    "ctg_bases_download", "ctg_bases_free", "ctg_bases_len", "ctg_bases_plan", "ctg_msm_g1", "ctg_msm_g2", "ctg_msm_g1_dev",
     "ctg_msm_g2_dev", "ctg_msm_g1_partial", "ctg_msm_g2_partial", "ctg_g1_combine", "ctg_g2_combine",
     "ctg_g1_combine_dev", "ctg_g2_combine_dev", "ctg_pk_upload", "ctg_pk_free", "ctg_r1cs_upload",
     "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch", "ctg_pk_upload_shard", "ctg_prove_partial",
@@ -53,6 +53,11 @@ class PkView(C.Structure):
 
 class Csr(C.Structure):
     _fields_ = [("row_ptr", C.c_void_p), ("col", C.c_void_p), ("val", C.c_void_p)]
+
+
+class MsmPlan(C.Structure):
+    _fields_ = [("window_bits", C.c_int32), ("windows", C.c_int32), ("copies", C.c_int32), ("bucket_sets", C.c_int32),
+                ("buckets_per_set", C.c_uint32)]
 
 
 class Timings(C.Structure):
@@ -101,6 +106,11 @@ class Bases:
 
     def __len__(self):
         return int(load().ctg_bases_len(self.handle))
+
+    def plan(self):
+        p = MsmPlan()
+        self.ctx._check(load().ctg_bases_plan(self.handle, C.byref(p)))
+        return {k: int(getattr(p, k)) for k, _ in MsmPlan._fields_}
 
     def download(self, first=0, count=None):
         count = len(self) - first if count is None else count

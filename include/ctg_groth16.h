@@ -149,6 +149,9 @@ int32_t ctg_bases_progression_g2(ctg_ctx* ctx, const ctg_g2_affine* g, const ctg
 int32_t ctg_bases_download(ctg_ctx* ctx, const ctg_bases* bases, uint64_t first, uint64_t count, void* host_points);
 void ctg_bases_free(ctg_ctx* ctx, ctg_bases* bases);
 uint64_t ctg_bases_len(const ctg_bases* bases);
+/* the MSM schedule chosen for this table: window bits c, windows ceil(256/c), precomputed copies kept, bucket sets */
+typedef struct { int32_t window_bits, windows, copies, bucket_sets; uint32_t buckets_per_set; } ctg_msm_plan;
+int32_t ctg_bases_plan(const ctg_bases* bases, ctg_msm_plan* out);
 
 /* sum_{i<n} scalars[i] * bases[i], n <= len(bases); affine result in host memory */
 int32_t ctg_msm_g1(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_affine* out);
