@@ -30,6 +30,7 @@ import numpy as np  # noqa: E402
 
 MAC32_PER_G1_POINT = 48_000      # 16 signed windows x (8M + 2S) x 300 MAC32 per Fq product
 MAC32_PER_MADD_EXECUTED = 2_844  # what the kernel executes per mixed addition: 8 products x 300 + one 2-product lazy reduction (444)
+OUT = sys.stdout
 METRIC = "g1_msm_throughput"
 UNIT = "Mpts/s"
 
@@ -138,11 +139,22 @@ def reference_arm(args):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": ark.threads(), "kind": "port",
                              "sample": f"arkworks-0.3.0 VariableBaseMSM algorithm restated in C++ (oracle/c), 2^{n.bit_length() - 1} points, input generation {gen_s:.1f}s untimed"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=OUT, flush=True)
+
+
+def claim_stdout():
+    """Keep a private handle on the real stdout for the ONE JSON line and point fd 1 at stderr, so that library chatter
+    (e.g. "NCCL version ..." printed by ncclCommInitRank) cannot land in front of it."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
 
 
 def main():
     args = parse()
+    global OUT
+    OUT = claim_stdout()
     if args.impl == "reference":
         reference_arm(args)
         return
@@ -274,7 +286,7 @@ def main():
         if not args.no_extras:
             line["extra"] = extras(ctx, torch, dev, stream, S, args)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=OUT, flush=True)
     bases.free()
     ctx.close()
     if world > 1:

@@ -281,6 +281,12 @@ void ctg_bases_free(ctg_ctx* ctx, ctg_bases* bases) {
   delete bases;
 }
 uint64_t ctg_bases_len(const ctg_bases* bases) { return bases ? bases->b.n : 0; }
+int32_t ctg_ctx_set_ba_levels(ctg_ctx* ctx, int levels) {
+  if (!ctx) return CTG_ERR_INVALID;
+  if (levels < -1 || levels > 6) return fail(ctx, CTG_ERR_INVALID, "ba_levels must be in [-1, 6]");
+  ctx->ba_levels = levels;
+  return CTG_OK;
+}
 int32_t ctg_bases_plan(const ctg_bases* bases, ctg_msm_plan* out) {
   if (!bases || !out) return CTG_ERR_INVALID;
   const MsmPlan& p = bases->b.plan;

@@ -36,6 +36,10 @@ struct MsmWorkspace {
   void* chunk = nullptr;        // bucket-reduction partials
   void* result = nullptr;       // 1 XYZZ
   uint32_t* tile_sums = nullptr;  // scan scratch
+  // batched-affine tree (msm_acc.cuh): compact point arrays of the odd / even levels and their bucket offsets
+  void* ba_pts[2] = {nullptr, nullptr};
+  uint32_t* ba_starts[2] = {nullptr, nullptr};   // [nb + 1] each
+  size_t cap_ba_bytes[2] = {0, 0}, cap_ba_nb = 0;
   size_t cap_nb = 0, cap_entries = 0, cap_bucket_bytes = 0, cap_part_bytes = 0, cap_chunk_bytes = 0;
   int part_threads = 0;
 };
@@ -78,6 +82,7 @@ struct ctg_ctx {
   bool own_stream = true;
   std::string last_error;
   uint64_t launches = 0;
+  int ba_levels = -1;   // batched-affine tree levels per MSM: -1 = chosen per call (msm.cuh ba_num_levels), 0..6 forced
   std::map<int, ctg::NttDomain> domains;
   ctg::MsmWorkspace ws[2];
   ctg::ProveLane lanes[ctg::kMaxLanes];

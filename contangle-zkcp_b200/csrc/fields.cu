@@ -12,6 +12,11 @@ template <class F, int OP> __global__ void field_op_kernel(const F* __restrict__
   F x = a[i], y = b[i];
   out[i] = OP == CTG_OP_MUL ? x * y : (OP == CTG_OP_ADD ? x + y : x - y);
 }
+template <class F> __global__ void __launch_bounds__(128) field_inv_kernel(const F* __restrict__ a, F* __restrict__ out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = a[i].inv_bingcd();
+}
 
 template <class F> static int32_t launch_op(ctg_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n, cudaStream_t st) {
   unsigned blocks = (unsigned)((n + 127) / 128);
@@ -20,6 +25,7 @@ template <class F> static int32_t launch_op(ctg_ctx* ctx, int op, const void* a,
     case CTG_OP_MUL: field_op_kernel<F, CTG_OP_MUL><<<blocks, 128, 0, st>>>(pa, pb, po, n); break;
     case CTG_OP_ADD: field_op_kernel<F, CTG_OP_ADD><<<blocks, 128, 0, st>>>(pa, pb, po, n); break;
     case CTG_OP_SUB: field_op_kernel<F, CTG_OP_SUB><<<blocks, 128, 0, st>>>(pa, pb, po, n); break;
+    case CTG_OP_INV: field_inv_kernel<F><<<blocks, 128, 0, st>>>(pa, po, n); break;
     default: return fail(ctx, CTG_ERR_INVALID, "field op: unknown op");
   }
   CTG_KERNEL_CHECK(ctx);

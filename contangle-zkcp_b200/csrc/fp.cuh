@@ -35,6 +35,10 @@ struct FrParams {
     constexpr uint32_t m[8] = {0xf3f29c6du, 0xc999e990u, 0x87925c23u, 0x2b6cedcbu, 0x7254398fu, 0x05d31496u, 0x9f59ff11u, 0x0748d9d9u};
     return m[i];
   }
+  CTG_HD static constexpr uint32_t inv_c(int i) {  // 2^(2 * 18) * R^3 mod r: closing constant of inv_bingcd (18 outer iterations)
+    constexpr uint32_t m[8] = {0xcb9d63b7u, 0x6e19d729u, 0x5f8be0ccu, 0xf8f3f232u, 0xa5edc8e5u, 0xbab78932u, 0xc66409cfu, 0x4a73978cu};
+    return m[i];
+  }
 };
 
 struct FqParams {
@@ -53,6 +57,11 @@ struct FqParams {
   CTG_HD static constexpr uint32_t r2(int i) {  // R^2 mod p
     constexpr uint32_t m[12] = {0x1c341746u, 0xf4df1f34u, 0x09d104f1u, 0x0a76e6a6u, 0x4c95b6d5u, 0x8de5476cu,
                                 0x939d83c0u, 0x67eb88a9u, 0xb519952du, 0x9a793e85u, 0x92cae3aau, 0x11988fe5u};
+    return m[i];
+  }
+  CTG_HD static constexpr uint32_t inv_c(int i) {  // 2^(2 * 26) * R^3 mod p: closing constant of inv_bingcd (26 outer iterations)
+    constexpr uint32_t m[12] = {0x8c5d1a2eu, 0x42957fa8u, 0x24cc85b1u, 0xa6507a62u, 0x39990a58u, 0xd8ca1b85u,
+                                0xac2f63fcu, 0xe65a054fu, 0xe1f35417u, 0x4ca0897au, 0xa0365c54u, 0x032748cbu};
     return m[i];
   }
 };
@@ -284,6 +293,149 @@ template <class P> struct alignas(16) Fp {
     }
     return acc;
   }
+
+  // a^-1 by binary GCD with 30-step inner loops on 62-bit approximations (T. Pornin, "Optimized Binary GCD for Modular
+  // Inversion", ePrint 2020/972, Algorithm 2, restated for 32-bit limbs).  About 12x cheaper than the Fermat ladder above and
+  // almost entirely shifts / adds, i.e. off the IMAD pipe; branch-free, so the lanes of a warp stay in lockstep.  Used by the
+  // batched-affine bucket accumulation (one inversion per batch of point additions).  inv_bingcd(0) = 0.
+  //   invariants (y = this image, m = modulus):  a * 2^(30 i) == u_nodiv * y,  b * 2^(30 i) == v_nodiv * y   (mod m)
+  //   u, v are divided by 2^32 per outer iteration (one Montgomery row), so after I iterations y^-1 = v * 2^(2 I); the closing
+  //   product with P::inv_c = 2^(2 I) R^3 also turns (x R)^-1 into the Montgomery image x^-1 R.
+  CTG_HD_COLD Fp inv_bingcd() const {
+    constexpr int J = 30;                                  // inner steps per outer iteration
+    constexpr int ITER = (2 * 32 * N - 1 + J - 1) / J;     // 2 len(m) - 1 steps suffice; 32 N >= len(m)
+    uint32_t a[N], b[N], u[N], vv[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) { a[i] = v[i]; b[i] = P::mod(i); u[i] = 0; vv[i] = 0; }
+    u[0] = 1;
+#pragma unroll 1
+    for (int it = 0; it < ITER; it++) {
+      // ---- 62-bit approximations: low 30 bits + the 32 bits below the top of max(len a, len b, 62)
+      uint32_t top = 0, tl = 0;
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const uint32_t w = a[i] | b[i];
+        const bool nz = w != 0;
+        top = nz ? w : top;
+        tl = nz ? (uint32_t)i : tl;
+      }
+#if defined(__CUDA_ARCH__)
+      uint32_t n = 32u * tl + 32u - (uint32_t)__clz((int)top);
+#else
+      uint32_t n = top ? 32u * tl + 32u - (uint32_t)__builtin_clz(top) : 0u;
+#endif
+      if (n < 62u) n = 62u;
+      const uint32_t p = n - 32u, w0 = p >> 5, r = p & 31u;
+      uint32_t a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const uint32_t m0 = (uint32_t)i == w0 ? 0xffffffffu : 0u;
+        const uint32_t m1 = (uint32_t)i == w0 + 1 ? 0xffffffffu : 0u;
+        a0 |= a[i] & m0; b0 |= b[i] & m0;
+        a1 |= a[i] & m1; b1 |= b[i] & m1;
+      }
+      const uint32_t ha = (uint32_t)(((((uint64_t)a1) << 32) | a0) >> r);
+      const uint32_t hb = (uint32_t)(((((uint64_t)b1) << 32) | b0) >> r);
+      uint64_t xa = (uint64_t)(a[0] & 0x3fffffffu) | ((uint64_t)ha << 30);
+      uint64_t xb = (uint64_t)(b[0] & 0x3fffffffu) | ((uint64_t)hb << 30);
+      // ---- 30 binary-GCD steps on the approximations, recording the transition matrix
+      uint32_t f0 = 1, g0 = 0, f1 = 0, g1 = 1;   // two's complement int32
+#pragma unroll 2
+      for (int j = 0; j < J; j++) {
+        const uint64_t odd = 0ull - (xa & 1ull);
+        const uint64_t sw = odd & (xa < xb ? ~0ull : 0ull);
+        const uint64_t t = (xa ^ xb) & sw;
+        xa ^= t; xb ^= t;
+        const uint32_t sw32 = (uint32_t)sw, odd32 = (uint32_t)odd;
+        const uint32_t tf = (f0 ^ f1) & sw32, tg = (g0 ^ g1) & sw32;
+        f0 ^= tf; f1 ^= tf; g0 ^= tg; g1 ^= tg;
+        xa -= xb & odd;
+        f0 -= f1 & odd32; g0 -= g1 & odd32;
+        xa >>= 1;
+        f1 <<= 1; g1 <<= 1;
+      }
+      // ---- (a, b) <- (f0 a + g0 b, f1 a + g1 b) / 2^30, made non-negative
+      int64_t F0 = (int32_t)f0, G0 = (int32_t)g0, F1 = (int32_t)f1, G1 = (int32_t)g1;
+      {
+        int64_t ca = 0, cb = 0;
+        uint32_t na[N + 1], nb[N + 1];
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+          const int64_t ai = (int64_t)(uint64_t)a[i], bi = (int64_t)(uint64_t)b[i];
+          ca += F0 * ai + G0 * bi;
+          cb += F1 * ai + G1 * bi;
+          na[i] = (uint32_t)ca; nb[i] = (uint32_t)cb;
+          ca >>= 32; cb >>= 32;
+        }
+        na[N] = (uint32_t)ca; nb[N] = (uint32_t)cb;
+        const uint32_t sa = ca < 0 ? 0xffffffffu : 0u, sb = cb < 0 ? 0xffffffffu : 0u;
+        // shift right by 30, then conditional two's-complement negation: x -> (x ^ s) - s
+        uint32_t bora = 0, borb = 0;   // running "+1" carries of the negation
+        bora = sa & 1u; borb = sb & 1u;
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+          const uint32_t xa32 = ((na[i] >> 30) | (na[i + 1] << 2)) ^ sa;
+          const uint32_t xb32 = ((nb[i] >> 30) | (nb[i + 1] << 2)) ^ sb;
+          const uint64_t ta = (uint64_t)xa32 + bora, tb = (uint64_t)xb32 + borb;
+          a[i] = (uint32_t)ta; b[i] = (uint32_t)tb;
+          bora = (uint32_t)(ta >> 32); borb = (uint32_t)(tb >> 32);
+        }
+        if (sa) { F0 = -F0; G0 = -G0; }
+        if (sb) { F1 = -F1; G1 = -G1; }
+      }
+      // ---- (u, v) <- (F0 u + G0 v, F1 u + G1 v) / 2^32 mod m, factors made non-negative by negating the operand
+      {
+        uint32_t nu[N], nv[N];
+        {
+          uint32_t bw = 0;
+          uint32_t zu = 0, zv = 0;
+#pragma unroll
+          for (int i = 0; i < N; i++) { zu |= u[i]; zv |= vv[i]; }
+          uint64_t t;
+          bw = 0;
+#pragma unroll
+          for (int i = 0; i < N; i++) { t = (uint64_t)P::mod(i) - u[i] - bw; nu[i] = zu ? (uint32_t)t : 0u; bw = (uint32_t)(t >> 63); }
+          bw = 0;
+#pragma unroll
+          for (int i = 0; i < N; i++) { t = (uint64_t)P::mod(i) - vv[i] - bw; nv[i] = zv ? (uint32_t)t : 0u; bw = (uint32_t)(t >> 63); }
+        }
+        const bool nF0 = F0 < 0, nG0 = G0 < 0, nF1 = F1 < 0, nG1 = G1 < 0;
+        const uint64_t f0u = (uint64_t)(nF0 ? -F0 : F0), g0u = (uint64_t)(nG0 ? -G0 : G0);
+        const uint64_t f1u = (uint64_t)(nF1 ? -F1 : F1), g1u = (uint64_t)(nG1 ? -G1 : G1);
+        uint32_t tu[N + 1], tv[N + 1];
+        uint64_t cu = 0, cv = 0;
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+          const uint64_t ua = nF0 ? nu[i] : u[i], va = nG0 ? nv[i] : vv[i];
+          const uint64_t ub = nF1 ? nu[i] : u[i], vb = nG1 ? nv[i] : vv[i];
+          cu += f0u * ua + g0u * va;     // < 2^30 * 2^32 + carry: no overflow
+          cv += f1u * ub + g1u * vb;
+          tu[i] = (uint32_t)cu; tv[i] = (uint32_t)cv;
+          cu >>= 32; cv >>= 32;
+        }
+        tu[N] = (uint32_t)cu; tv[N] = (uint32_t)cv;
+        // one Montgomery row each: (t + q m) / 2^32 < 2 m, then a conditional subtraction
+        const uint32_t qu = tu[0] * P::INV, qv = tv[0] * P::INV;
+        cu = ((uint64_t)tu[0] + (uint64_t)qu * P::mod(0)) >> 32;
+        cv = ((uint64_t)tv[0] + (uint64_t)qv * P::mod(0)) >> 32;
+#pragma unroll
+        for (int i = 1; i < N; i++) {
+          cu += (uint64_t)tu[i] + (uint64_t)qu * P::mod(i);
+          cv += (uint64_t)tv[i] + (uint64_t)qv * P::mod(i);
+          u[i - 1] = (uint32_t)cu; vv[i - 1] = (uint32_t)cv;
+          cu >>= 32; cv >>= 32;
+        }
+        u[N - 1] = (uint32_t)(cu + tu[N]);
+        vv[N - 1] = (uint32_t)(cv + tv[N]);
+        reduce_once(u);
+        reduce_once(vv);
+      }
+    }
+    Fp res, c;
+#pragma unroll
+    for (int i = 0; i < N; i++) { res.v[i] = vv[i]; c.v[i] = P::inv_c(i); }
+    return res * c;
+  }
 };
 
 typedef Fp<FrParams> Fr;
@@ -319,6 +471,10 @@ struct Fq2 {
   }
   CTG_HD Fq2 inv() const {
     Fq n = (c0.sqr() + c1.sqr()).inv();
+    return {c0 * n, (c1 * n).neg()};
+  }
+  CTG_HD Fq2 inv_bingcd() const {
+    Fq n = (c0.sqr() + c1.sqr()).inv_bingcd();
     return {c0 * n, (c1 * n).neg()};
   }
 };

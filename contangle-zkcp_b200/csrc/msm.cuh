@@ -19,6 +19,8 @@
 // doubling chain at the end.
 #pragma once
 #include "ctg_internal.h"
+#include <cstdlib>
+
 #include "msm_digits.cuh"
 
 namespace ctg {
@@ -171,8 +173,25 @@ template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict
 // ---- 4. bucket accumulation (dominant kernel): msm_acc.cuh, compiled in its own translation unit
 template <class F> int accumulate_max_blocks_per_sm();
 template <class F>
-void accumulate_launch(int blocks, cudaStream_t st, const Affine<F>* bases, const uint32_t* entries, const uint32_t* starts, uint32_t nb,
+void accumulate_launch(int blocks, cudaStream_t st, bool direct, const Affine<F>* bases, const uint32_t* entries, const uint32_t* starts, uint32_t nb,
                        XYZZ<F>* buckets, XYZZ<F>* part_pt, uint32_t* part_gb);
+// batched-affine tree levels in front of it (msm_acc.cuh, stage 4a)
+template <class F> int ba_max_blocks_per_sm();
+template <class F> void ba_scan_launch(cudaStream_t st, const uint32_t* in_starts, uint32_t* out_starts, uint32_t nb, uint32_t* tile_sums);
+template <class F>
+void ba_level_launch(int blocks, cudaStream_t st, bool first, const Affine<F>* bases, const uint32_t* entries, const Affine<F>* in_pts,
+                     const uint32_t* in_starts, const uint32_t* out_starts, uint32_t nb, Affine<F>* out_pts);
+// Number of tree levels for an MSM with `entries` bucket entries, `nb` buckets and `threads` level-kernel threads: a level pays
+// while a thread still has >= 24 pairs to share an inversion over and buckets still hold several points.  CTG_BA_LEVELS overrides.
+inline int ba_num_levels(uint64_t entries, uint64_t nb, uint64_t threads) {
+  static int forced = -2;
+  if (forced == -2) { const char* e = getenv("CTG_BA_LEVELS"); forced = e ? atoi(e) : -1; }
+  if (forced >= 0) return forced > 6 ? 6 : forced;
+  int L = 0;
+  uint64_t m = entries;
+  while (L < 4 && (m / 2) / threads >= 24 && m / nb >= 3) { m = m / 2 + nb / 2; L++; }
+  return L;
+}
 
 // ---- 5. buckets cut by slice boundaries -------------------------------------------------------
 template <class F> __device__ __forceinline__ XYZZ<F> warp_sum(XYZZ<F> acc, XYZZ<F>* sh /* 32 per warp */, unsigned lane) {
@@ -444,7 +463,7 @@ template <class F, int MAXC> __global__ void __launch_bounds__(128) precompute_k
 // ---- host orchestration -------------------------------------------------------------------------
 template <class F> struct MsmHost {
 
-  static int32_t ensure_ws(ctg_ctx* ctx, MsmWorkspace& ws, const MsmPlan& plan, uint64_t n, int max_threads) {
+  static int32_t ensure_ws(ctg_ctx* ctx, MsmWorkspace& ws, const MsmPlan& plan, uint64_t n, int max_threads, int ba_levels) {
     const size_t nb = (size_t)plan.nsets * plan.nbuckets_per_set;
     const size_t ne = (size_t)n * plan.nwin;
     if (nb + 1 > ws.cap_nb) {
@@ -481,6 +500,26 @@ template <class F> struct MsmHost {
       CTG_CUDA(ctx, cudaMalloc(&ws.chunk, cb));
       ws.cap_chunk_bytes = cb;
     }
+    if (ba_levels > 0) {
+      // level l holds at most ne / 2^l + nb points (every bucket rounds up once per level)
+      const size_t need[2] = {(ne / 2 + nb + 1) * sizeof(Affine<F>), (ne / 4 + nb + 1) * sizeof(Affine<F>)};
+      for (int k = 0; k < 2; k++) {
+        if (k == 1 && ba_levels < 2) break;
+        if (need[k] > ws.cap_ba_bytes[k]) {
+          if (ws.ba_pts[k]) cudaFree(ws.ba_pts[k]);
+          ws.ba_pts[k] = nullptr; ws.cap_ba_bytes[k] = 0;
+          if (cudaMalloc(&ws.ba_pts[k], need[k]) != cudaSuccess) { cudaGetLastError(); return fail(ctx, CTG_ERR_OOM, "msm: out of device memory for the batched-affine level arrays"); }
+          ws.cap_ba_bytes[k] = need[k];
+        }
+      }
+      if (nb + 1 > ws.cap_ba_nb) {
+        for (int k = 0; k < 2; k++) {
+          if (ws.ba_starts[k]) cudaFree(ws.ba_starts[k]);
+          CTG_CUDA(ctx, cudaMalloc(&ws.ba_starts[k], (nb + 1) * sizeof(uint32_t)));
+        }
+        ws.cap_ba_nb = nb + 1;
+      }
+    }
     if (!ws.result) CTG_CUDA(ctx, cudaMalloc(&ws.result, sizeof(XYZZ<Fq2>)));
     if (!ws.tile_sums) CTG_CUDA(ctx, cudaMalloc(&ws.tile_sums, 1025 * sizeof(uint32_t)));
     return CTG_OK;
@@ -497,15 +536,19 @@ template <class F> struct MsmHost {
       return CTG_OK;
     }
     // accumulate launch geometry
-    static int occ = 0;
+    static int occ = 0, ba_occ = 0;
     if (!occ) {
       occ = accumulate_max_blocks_per_sm<F>();
       if (occ < 1) occ = 1;
+      ba_occ = ba_max_blocks_per_sm<F>();
+      if (ba_occ < 1) ba_occ = 1;
     }
     const int max_blocks = ctx->sm_count * occ;
     const int max_threads = max_blocks * 128;
-    CTG_TRY(ensure_ws(ctx, ws, plan, n, max_threads));
     const uint32_t nb = (uint32_t)plan.nsets * plan.nbuckets_per_set;
+    const int ba_blocks = ctx->sm_count * ba_occ;
+    const int ba_levels = ctx->ba_levels >= 0 ? (ctx->ba_levels > 6 ? 6 : ctx->ba_levels) : ba_num_levels((uint64_t)n * plan.nwin, nb, (uint64_t)ba_blocks * 128);
+    CTG_TRY(ensure_ws(ctx, ws, plan, n, max_threads, ba_levels));
     XYZZ<F>* buckets = reinterpret_cast<XYZZ<F>*>(ws.buckets);
     XYZZ<F>* part_pt = reinterpret_cast<XYZZ<F>*>(ws.part_pt);
     XYZZ<F>* chunk = reinterpret_cast<XYZZ<F>*>(ws.chunk);
@@ -533,11 +576,27 @@ template <class F> struct MsmHost {
     if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
 
     CTG_CUDA(ctx, cudaMemsetAsync(ws.buckets, 0, (size_t)nb * sizeof(XYZZ<F>), st));
-    uint64_t want_threads = ((uint64_t)n * plan.nwin + 15) / 16;
+    // 4a. batched-affine tree levels: level l reads level l-1 (level 1 the bases through the entry list)
+    const uint32_t* cur_starts = ws.counts;
+    const Affine<F>* cur_pts = nullptr;
+    for (int l = 1; l <= ba_levels; l++) {
+      uint32_t* out_starts = ws.ba_starts[(l - 1) & 1];
+      Affine<F>* out_pts = reinterpret_cast<Affine<F>*>(ws.ba_pts[(l - 1) & 1]);
+      ba_scan_launch<F>(st, cur_starts, out_starts, nb, ws.tile_sums);
+      ctx->launches += 2;
+      CTG_KERNEL_CHECK(ctx);
+      ba_level_launch<F>(ba_blocks, st, l == 1, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, cur_pts, cur_starts, out_starts, nb, out_pts);
+      CTG_KERNEL_CHECK(ctx);
+      cur_starts = out_starts;
+      cur_pts = out_pts;
+    }
+    // 4b. XYZZ accumulation of what is left
+    uint64_t want_threads = ((((uint64_t)n * plan.nwin) >> ba_levels) + 15) / 16;
     int blocks = (int)std::min<uint64_t>((want_threads + 127) / 128, (uint64_t)max_blocks);
     if (blocks < 1) blocks = 1;
     const uint32_t nslots = (uint32_t)blocks * 128 * 2;
-    accumulate_launch<F>(blocks, st, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, ws.counts, nb, buckets, part_pt, ws.part_gb);
+    if (ba_levels > 0) accumulate_launch<F>(blocks, st, true, cur_pts, nullptr, cur_starts, nb, buckets, part_pt, ws.part_gb);
+    else accumulate_launch<F>(blocks, st, false, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, ws.counts, nb, buckets, part_pt, ws.part_gb);
     CTG_KERNEL_CHECK(ctx);
     msm_fixup_short_kernel<F><<<(nslots + 127) / 128, 128, 0, st>>>(part_pt, ws.part_gb, nslots, buckets);
     CTG_KERNEL_CHECK(ctx);

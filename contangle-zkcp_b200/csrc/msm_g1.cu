@@ -57,7 +57,8 @@ int32_t g1_combine_dev(ctg_ctx* ctx, const G1XYZZ* d_in, uint32_t k, G1Affine* d
 }
 
 void msm_ws_free(MsmWorkspace& ws) {
-  void* ptrs[] = {ws.counts, ws.cursor, ws.entries, ws.buckets, ws.part_pt, ws.part_gb, ws.chunk, ws.result, ws.tile_sums};
+  void* ptrs[] = {ws.counts, ws.cursor, ws.entries, ws.buckets, ws.part_pt, ws.part_gb, ws.chunk, ws.result, ws.tile_sums,
+                  ws.ba_pts[0], ws.ba_pts[1], ws.ba_starts[0], ws.ba_starts[1]};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   ws = MsmWorkspace();

@@ -21,11 +21,11 @@ FR_W, FQ_W, G1_W, G2_W = 8, 12, 24, 48
 PARTIAL_W = 4 * 2 * G1_W + 2 * G2_W   # ctg_proof_partial: 4 G1 XYZZ + 1 G2 XYZZ = 288 words (1152 B)
 SCALARS_CANONICAL, SCALARS_MONT, MSM_TIMED = 0, 1, 0x100
 FIELD_FR, FIELD_FQ, FIELD_FQ2 = 0, 1, 2
-OP_MUL, OP_ADD, OP_SUB = 0, 1, 2
+OP_MUL, OP_ADD, OP_SUB, OP_INV = 0, 1, 2, 3
 
 # every symbol include/ctg_groth16.h declares (checked by tests/test_abi_cpu.py)
 EXPORTS = [
-    "ctg_ctx_create", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_sync", "ctg_launch_count",
+    "ctg_ctx_create", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_ctx_set_ba_levels", "ctg_sync", "ctg_launch_count",
     "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch",
     "ctg_fr_mul_batch", "ctg_fq_mul_batch", "ctg_imad_peak_probe", "ctg_ntt_fr", "ctg_ntt_fr_dev",
     "ctg_bases_upload_g1", "ctg_bases_upload_g2", "ctg_bases_progression_g1", "ctg_bases_progression_g2",
@@ -159,6 +159,10 @@ class Context:
         return t.as_dict()
 
     # ---- fields
+    def set_ba_levels(self, levels=-1):
+        """MSM bucket accumulation: number of batched-affine tree levels (-1 = automatic, 0 = XYZZ only)."""
+        self._check(load().ctg_ctx_set_ba_levels(self.h, int(levels)))
+
     def field_op(self, field, op, a, b):
         w = {FIELD_FR: FR_W, FIELD_FQ: FQ_W, FIELD_FQ2: 2 * FQ_W}[field]
         a, b = _arr(a, w), _arr(b, w)

@@ -108,6 +108,10 @@ const char* ctg_last_error(ctg_ctx* ctx);
 /* Run all work of this context on a caller-owned cudaStream_t (e.g. torch's current stream). */
 int32_t ctg_ctx_set_stream(ctg_ctx* ctx, void* cuda_stream);
 int32_t ctg_sync(ctg_ctx* ctx);
+/* Bucket accumulation schedule of the MSMs: `levels` pairwise batched-affine tree levels (5M + 1S per addition, one shared
+ * binary-GCD inversion per 64 additions) before the XYZZ accumulation (8M + 2S).  -1 (default) = chosen per call from the
+ * size; 0 = XYZZ only; 1..6 forced (tests, sweeps).  The result is the same group element either way. */
+int32_t ctg_ctx_set_ba_levels(ctg_ctx* ctx, int levels);
 uint64_t ctg_launch_count(ctg_ctx* ctx); /* kernels launched by this context so far */
 int32_t ctg_last_timings(ctg_ctx* ctx, ctg_timings* out);
 
@@ -125,6 +129,7 @@ int32_t ctg_d2h(ctg_ctx* ctx, void* h_dst, const void* d_src, size_t bytes);
 #define CTG_OP_MUL 0
 #define CTG_OP_ADD 1
 #define CTG_OP_SUB 2
+#define CTG_OP_INV 3 /* out[i] = a[i]^-1 (b ignored, may equal a); 0 -> 0.  The binary-GCD inversion the batched-affine MSM uses */
 /* out[i] = a[i] (op) b[i]; host buffers of n elements (32 / 48 / 96 bytes each) */
 int32_t ctg_field_op_batch(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n);
 int32_t ctg_fr_mul_batch(ctg_ctx* ctx, const ctg_fr* a, const ctg_fr* b, ctg_fr* out, size_t n);

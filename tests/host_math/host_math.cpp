@@ -21,6 +21,9 @@ void hm_fq2_mul2_sub(const Fq2* a, const Fq2* b, const Fq2* c, const Fq2* d, Fq2
 void hm_fr_from_mont(const Fr* a, Fr* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].from_mont(); }
 void hm_fr_to_mont(const Fr* a, Fr* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].to_mont(); }
 void hm_fq_inv(const Fq* a, Fq* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].inv(); }
+void hm_fq_inv_bingcd(const Fq* a, Fq* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].inv_bingcd(); }
+void hm_fr_inv_bingcd(const Fr* a, Fr* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].inv_bingcd(); }
+void hm_fq2_inv_bingcd(const Fq2* a, Fq2* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].inv_bingcd(); }
 // sum of points with per-point sign through the XYZZ mixed addition, then affine
 void hm_g1_sum(const G1Affine* p, const uint8_t* neg, uint64_t n, G1Affine* out) {
   G1XYZZ acc = G1XYZZ::inf();

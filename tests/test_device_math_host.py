@@ -73,6 +73,31 @@ def test_fq2_and_inverse(hm):
     assert np.array_equal(ark.fq_mul(x, inv), one)
 
 
+@pytest.mark.parametrize("field", ["fr", "fq"])
+def test_bingcd_inverse_matches_pow(hm, field):
+    """inv_bingcd (Pornin's binary GCD, the inversion of the batched-affine MSM) against x^(p-2) in Python."""
+    mod, w, R = (B.R_MOD, 8, B.FR_R) if field == "fr" else (B.P_MOD, 12, B.FQ_R)
+    vals = _edge(mod, 400) + [(1 << 62) - 1, 1 << 61, 3] + [rnd.randrange(1 << k) % mod for k in range(1, w * 32 - 2, 5)]
+    a = ark.ints_to_words(vals, w)
+    out = np.zeros_like(a)
+    getattr(hm, f"hm_{field}_inv_bingcd")(_p(a), _p(out), C.c_uint64(len(vals)))
+    rinv = pow(R, -1, mod)
+    want = [0 if v == 0 else pow(v * rinv % mod, -1, mod) * R % mod for v in vals]   # image of the inverse of the value a is the image of
+    assert ark.words_to_ints(out) == want
+
+
+def test_fq2_bingcd_inverse(hm):
+    n = 16
+    a = ark.ints_to_words([rnd.randrange(B.P_MOD) for _ in range(2 * n)], 12).reshape(n, 24)
+    a[3] = 0
+    inv = np.zeros_like(a)
+    hm.hm_fq2_inv_bingcd(_p(a), _p(inv), C.c_uint64(n))
+    one = np.zeros_like(a)
+    one[:, :12] = ark.fq_to_mont(ark.ints_to_words([1], 12))[0]
+    one[3] = 0
+    assert np.array_equal(ark.fq2_mul(a, inv), one)
+
+
 def test_xyzz_sum_with_special_cases(hm):
     a, b = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
     n = 24

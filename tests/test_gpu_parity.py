@@ -46,6 +46,15 @@ def test_field_ops(ctx, field, w, mod):
     assert np.array_equal(ctx.fr_mul(a[:, :8], b[:, :8]) if w == 8 else ctx.fq_mul(a, b), getattr(ark, f"{name}_mul")(a, b))
 
 
+@pytest.mark.parametrize("field,w,mod,R", [(ctg.FIELD_FR, 8, B.R_MOD, B.FR_R), (ctg.FIELD_FQ, 12, B.P_MOD, B.FQ_R)])
+def test_field_inverse_bingcd(ctx, field, w, mod, R):
+    vals = _edge(mod, 1000) + [rnd.randrange(1 << k) % mod for k in range(1, w * 32 - 2, 3)]
+    a = ark.ints_to_words(vals, w)
+    got = ark.words_to_ints(ctx.field_op(field, ctg.OP_INV, a, a))
+    rinv = pow(R, -1, mod)
+    assert got == [0 if v == 0 else pow(v * rinv % mod, -1, mod) * R % mod for v in vals]
+
+
 def test_fq2_mul(ctx):
     n = 3000
     a = ark.ints_to_words([rnd.randrange(B.P_MOD) for _ in range(2 * n)], 12).reshape(n, 24)
@@ -158,6 +167,57 @@ def test_msm_g1_window_and_precompute_choices(ctx, c_bits, copies):
     t = ctx.bases_g1(pts, copies=copies, c_bits=c_bits)
     assert np.array_equal(ctx.msm(t, sc), ark.msm_g1(pts, sc)), (c_bits, copies)
     t.free()
+
+
+# ---- batched-affine tree levels (msm_acc.cuh stage 4a): forced on small inputs, every pair kind ----
+@pytest.mark.parametrize("levels", [1, 2, 3, 6])
+@pytest.mark.parametrize("kind", ["uniform", "poe", "equal", "duplicates", "cancel", "inf", "tiny"])
+def test_msm_g1_batched_affine_levels(ctx, levels, kind):
+    n = 2500 if kind != "tiny" else 3
+    pts = _g1_bases(n, 41)
+    sc = ark.random_scalars_canon(n, 43, kind if kind in ("uniform", "poe", "equal") else "uniform")
+    if kind == "duplicates":      # equal points with equal scalars share every bucket: tangent (doubling) pairs at every level
+        pts[:] = pts[0]
+        sc[:] = sc[0]
+    elif kind == "cancel":        # P and -P with the same scalar sit next to each other in every bucket: chord through infinity
+        neg = ark.g1_from_py([B.G1.neg(P) for P in ark.g1_to_py(pts[0::2])])
+        pts[1::2] = neg[: pts[1::2].shape[0]]
+        sc[1::2] = sc[0::2][: sc[1::2].shape[0]]
+        sc[-1] = sc[0]            # one survivor so that the total is not the identity
+    elif kind == "inf":
+        pts[::3] = 0
+    ctx.set_ba_levels(levels)
+    try:
+        for c_bits in (4, 9):     # 8 / 256 buckets per window: deep and shallow trees
+            t = ctx.bases_g1(pts, copies=1, c_bits=c_bits)
+            assert np.array_equal(ctx.msm(t, sc), ark.msm_g1(pts, sc)), (kind, levels, c_bits)
+            t.free()
+    finally:
+        ctx.set_ba_levels(-1)
+
+
+@pytest.mark.parametrize("levels", [1, 3])
+@pytest.mark.parametrize("kind", ["uniform", "duplicates", "cancel"])
+def test_msm_g2_batched_affine_levels(ctx, levels, kind):
+    n = 700
+    pts = ark.g2_progression(ark.g2_generator(), fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD)), n)
+    sc = ark.random_scalars_canon(n, 47, "uniform")
+    pts[5] = 0
+    if kind == "duplicates":
+        pts[:] = pts[0]
+        sc[:] = sc[0]
+    elif kind == "cancel":
+        neg = ark.g2_from_py([B.G2.neg(P) for P in ark.g2_to_py(pts[0::2])])
+        pts[1::2] = neg
+        sc[1::2] = sc[0::2]
+        sc[-1] = sc[0]
+    ctx.set_ba_levels(levels)
+    try:
+        t = ctx.bases_g2(pts, copies=2, c_bits=5)
+        assert np.array_equal(ctx.msm(t, sc), ark.msm_g2(pts, sc)), (kind, levels)
+        t.free()
+    finally:
+        ctx.set_ba_levels(-1)
 
 
 def test_msm_g1_prefix_and_errors(ctx):
