@@ -181,15 +181,20 @@ template <class F> void ba_scan_launch(cudaStream_t st, const uint32_t* in_start
 template <class F>
 void ba_level_launch(int blocks, cudaStream_t st, bool first, const Affine<F>* bases, const uint32_t* entries, const Affine<F>* in_pts,
                      const uint32_t* in_starts, const uint32_t* out_starts, uint32_t nb, Affine<F>* out_pts);
-// Number of tree levels for an MSM with `entries` bucket entries, `nb` buckets and `threads` level-kernel threads: a level pays
-// while a thread still has >= 24 pairs to share an inversion over and buckets still hold several points.  CTG_BA_LEVELS overrides.
-inline int ba_num_levels(uint64_t entries, uint64_t nb, uint64_t threads) {
+// Number of tree levels for an MSM with `entries` bucket entries, `nb` buckets and `threads` level-kernel threads.
+// A level pays while a thread still has >= 24 pairs to share an inversion over and buckets still hold several points -- and only
+// over Fq2 (G2).  Measured on B200 (profiles/r01_batched_affine.txt): level 1 must gather every operand TWICE (denominators,
+// then the additions), and random 96-byte gathers from a multi-GB table top out at 12-15 G/s (tools/gather_probe.cu), so for
+// G1 (6 Fq products per addition) the level is gather-bound and no faster than the XYZZ kernel it replaces, while for G2
+// (17 Fq products per addition against 28) it wins.  ctg_ctx_set_ba_levels / CTG_BA_LEVELS force a count for either group.
+inline int ba_num_levels(uint64_t entries, uint64_t nb, uint64_t threads, size_t field_bytes) {
   static int forced = -2;
   if (forced == -2) { const char* e = getenv("CTG_BA_LEVELS"); forced = e ? atoi(e) : -1; }
   if (forced >= 0) return forced > 6 ? 6 : forced;
+  if (field_bytes <= 48) return 0;
   int L = 0;
   uint64_t m = entries;
-  while (L < 4 && (m / 2) / threads >= 24 && m / nb >= 3) { m = m / 2 + nb / 2; L++; }
+  while (L < 3 && (m / 2) / threads >= 24 && m / nb >= 3) { m = m / 2 + nb / 2; L++; }
   return L;
 }
 
@@ -547,7 +552,7 @@ template <class F> struct MsmHost {
     const int max_threads = max_blocks * 128;
     const uint32_t nb = (uint32_t)plan.nsets * plan.nbuckets_per_set;
     const int ba_blocks = ctx->sm_count * ba_occ;
-    const int ba_levels = ctx->ba_levels >= 0 ? (ctx->ba_levels > 6 ? 6 : ctx->ba_levels) : ba_num_levels((uint64_t)n * plan.nwin, nb, (uint64_t)ba_blocks * 128);
+    const int ba_levels = ctx->ba_levels >= 0 ? (ctx->ba_levels > 6 ? 6 : ctx->ba_levels) : ba_num_levels((uint64_t)n * plan.nwin, nb, (uint64_t)ba_blocks * 128, sizeof(F));
     CTG_TRY(ensure_ws(ctx, ws, plan, n, max_threads, ba_levels));
     XYZZ<F>* buckets = reinterpret_cast<XYZZ<F>*>(ws.buckets);
     XYZZ<F>* part_pt = reinterpret_cast<XYZZ<F>*>(ws.part_pt);
