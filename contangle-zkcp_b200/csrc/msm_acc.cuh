@@ -58,6 +58,38 @@ template <class F> __global__ void __launch_bounds__(256) ba_scan_apply_kernel(c
   if (blockIdx.x == 0 && tid == 0) out_starts[nb] = tile_sums[ntiles];
 }
 
+// ---- compact mixed addition: the field products are CALLS into one out-of-line copy each instead of ten inlined 400-instruction
+// bodies, so the accumulate loop is ~20 KB of SASS instead of ~64 KB and stays resident in the instruction caches
+// (profiles/r01_msm_accumulate_g1_ncu.txt: sm__icc_request_hit_rate 84.7 %, no_instruction stalls 0.46 per issue with the inlined body).
+template <class F> __device__ __noinline__ F fmul_call(const F a, const F b) { return a * b; }
+template <class F> __device__ __noinline__ F fmul2_sub_call(const F a, const F b, const F c, const F d) { return F::mul2_sub(a, b, c, d); }
+template <class F> __device__ __forceinline__ XYZZ<F> xyzz_madd_compact(const XYZZ<F>& acc, const Affine<F>& q_in, bool neg) {
+  if (q_in.is_inf()) return acc;
+  Affine<F> q = q_in;
+  if (neg) q.y = q.y.neg();
+  if (acc.is_inf()) return {q.x, q.y, F::one(), F::one()};
+  F U2 = fmul_call(q.x, acc.ZZ), S2 = fmul_call(q.y, acc.ZZZ);
+  F P = U2 - acc.X, R = S2 - acc.Y;
+  if (P.is_zero()) {
+    if (R.is_zero()) return xyzz_dbl_affine(q);
+    return XYZZ<F>::inf();
+  }
+  F PP = fmul_call(P, P), PPP = fmul_call(P, PP), Q = fmul_call(acc.X, PP);
+  XYZZ<F> r;
+  r.X = fmul_call(R, R) - PPP - Q.dbl();
+  r.Y = fmul2_sub_call(R, Q - r.X, acc.Y, PPP);
+  r.ZZ = fmul_call(acc.ZZ, PP);
+  r.ZZZ = fmul_call(acc.ZZZ, PPP);
+  return r;
+}
+
+// field product for the big kernels: inlined for Fq, a call for Fq2 (whose inlined body is three times the size)
+template <class F> struct AccCfg { static constexpr bool kCompact = sizeof(F) > 48; };
+template <class F> __device__ __forceinline__ F fm(const F& a, const F& b) {
+  if (AccCfg<F>::kCompact) return fmul_call(a, b);
+  return a * b;
+}
+
 // ---- 4a. one level of the pairwise affine tree -----------------------------------------------------
 // Pair classification (recomputed in both passes from the operands, no mults):
 //   kCopy1 / kCopy2 : the other operand is missing (odd count) or the point at infinity -> result = the present one
@@ -129,7 +161,7 @@ __global__ void __launch_bounds__(128) ba_level_kernel(const Affine<F>* __restri
       F d;
       ba_classify(p1, p2, has2, d);
       prefix[o - blo] = run;
-      run = run * d;
+      run = fm(run, d);
     }
     F inv = run.inv_bingcd();
     // ---- backward: peel the inverses off, finish the additions
@@ -139,16 +171,16 @@ __global__ void __launch_bounds__(128) ba_level_kernel(const Affine<F>* __restri
       const bool has2 = load_pair(o, p1, p2);
       F d;
       const int kind = ba_classify(p1, p2, has2, d);
-      const F dinv = inv * prefix[o - blo];
-      inv = inv * d;
+      const F dinv = fm(inv, prefix[o - blo]);
+      inv = fm(inv, d);
       Affine<F> r;
       if (kind == kAdd || kind == kDbl) {
         F num;
         if (kind == kAdd) num = p2.y - p1.y;
         else { F xx = p1.x.sqr(); num = xx.dbl() + xx; }
-        const F lam = num * dinv;
-        r.x = lam.sqr() - p1.x - p2.x;
-        r.y = lam * (p1.x - r.x) - p1.y;
+        const F lam = fm(num, dinv);
+        r.x = fm(lam, lam) - p1.x - p2.x;
+        r.y = fm(lam, p1.x - r.x) - p1.y;
       } else if (kind == kCopy1) r = p1;
       else if (kind == kCopy2) r = p2;
       else r = Affine<F>::inf();
@@ -161,7 +193,7 @@ __global__ void __launch_bounds__(128) ba_level_kernel(const Affine<F>* __restri
 // ---- 4b. bucket accumulation over what the tree left ------------------------------------------------
 // DIRECT = false: the list is entries[] (point index | sign << 31) into bases[]; DIRECT = true: the list is the
 // compact point array of the last tree level (bases = that array, entries unused).
-template <class F, bool DIRECT>
+template <class F, bool DIRECT, bool COMPACT>
 __global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                              const uint32_t* __restrict__ starts, uint32_t nb, XYZZ<F>* buckets,
                                                              XYZZ<F>* part_pt, uint32_t* part_gb) {
@@ -211,25 +243,37 @@ __global__ void __launch_bounds__(128) msm_accumulate_kernel(const Affine<F>* __
       do { gb++; bucket_begin = bucket_end; bucket_end = starts[gb + 1]; } while (bucket_end <= pos);
       seg_end = bucket_end < hi ? bucket_end : hi;
     }
-    acc = xyzz_madd(acc, P, !DIRECT && (e >> 31) != 0);
+    if (COMPACT) acc = xyzz_madd_compact(acc, P, !DIRECT && (e >> 31) != 0);
+    else acc = xyzz_madd(acc, P, !DIRECT && (e >> 31) != 0);
     e = e_next;
     P = P_next;
   }
   flush();
 }
 
+template <class F> inline bool acc_compact() {   // default per field; CTG_ACC_COMPACT=0/1 overrides (sweeps)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CTG_ACC_COMPACT"); v = e ? atoi(e) : (AccCfg<F>::kCompact ? 1 : 0); }
+  return v != 0;
+}
 static constexpr int kBaBatch = 64;   // pairs per shared inversion (local-memory prefix array of 64 field elements per thread)
 
 template <class F> int accumulate_max_blocks_per_sm() {
   int occ = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, msm_accumulate_kernel<F, false>, 128, 0) != cudaSuccess) return 1;
+  if (acc_compact<F>()) { if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, msm_accumulate_kernel<F, false, true>, 128, 0) != cudaSuccess) return 1; }
+  else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, msm_accumulate_kernel<F, false, false>, 128, 0) != cudaSuccess) return 1;
   return occ;
 }
 template <class F>
 void accumulate_launch(int blocks, cudaStream_t st, bool direct, const Affine<F>* bases, const uint32_t* entries, const uint32_t* starts, uint32_t nb,
                        XYZZ<F>* buckets, XYZZ<F>* part_pt, uint32_t* part_gb) {
-  if (direct) msm_accumulate_kernel<F, true><<<blocks, 128, 0, st>>>(bases, entries, starts, nb, buckets, part_pt, part_gb);
-  else msm_accumulate_kernel<F, false><<<blocks, 128, 0, st>>>(bases, entries, starts, nb, buckets, part_pt, part_gb);
+  if (acc_compact<F>()) {
+    if (direct) msm_accumulate_kernel<F, true, true><<<blocks, 128, 0, st>>>(bases, entries, starts, nb, buckets, part_pt, part_gb);
+    else msm_accumulate_kernel<F, false, true><<<blocks, 128, 0, st>>>(bases, entries, starts, nb, buckets, part_pt, part_gb);
+  } else {
+    if (direct) msm_accumulate_kernel<F, true, false><<<blocks, 128, 0, st>>>(bases, entries, starts, nb, buckets, part_pt, part_gb);
+    else msm_accumulate_kernel<F, false, false><<<blocks, 128, 0, st>>>(bases, entries, starts, nb, buckets, part_pt, part_gb);
+  }
 }
 template <class F> int ba_max_blocks_per_sm() {
   int o1 = 0, o2 = 0;
