@@ -358,6 +358,7 @@ def extras(ctx, torch, dev, stream, S, args):
         dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], copies=args.copies)
         dr = ctx.upload_r1cs(r1cs)
         del pk
+        zm = ctx.pinned_like(zm)      # the assignment sits in page-locked memory (ctg_host_alloc), as the Rust shim packs it
         r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
         for _ in range(2):
             ctx.prove(dpk, dr, zm, r, s)
@@ -370,6 +371,7 @@ def extras(ctx, torch, dev, stream, S, args):
         wall, tm = ts[len(ts) // 2]
         out[f"groth16_prove_mulchain_2^{lg}"] = {"wall_ms_median": wall, "stages_ms": {k: v for k, v in tm.items() if not k.startswith("msm_sort") and not k.startswith("msm_acc") and not k.startswith("msm_red")},
                                                  "note": "the five MSMs run on five streams: stage times overlap and do not add up to total_ms"}
+        ctx.pinned_free(zm)
         dpk.free(); dr.free()
     # config 5 shape at one GPU: batched PoE-shaped proofs with a device-resident key (proofs/s)
     for n_data in (1, 100):

@@ -66,6 +66,76 @@ static int32_t msm_check(ctg_ctx* ctx, const ctg_bases* bases, int group, uint64
   if (n > bases->b.n) return fail(ctx, CTG_ERR_INVALID, "msm: more scalars than bases");
   return CTG_OK;
 }
+// ---- split MSM ---------------------------------------------------------------------------------------
+// A large MSM is cut into point-range parts, each a complete MSM (sort, accumulate, reduce) on its own stream and workspace;
+// the partial sums are added at the end.  The accumulate kernels fill the GPU one after the other, while the other parts'
+// scalar uploads (host entry points), bucket sorts (HBM / atomics) and latency-bound bucket reductions run beside them.
+// The same overlap the prover gets from running its five MSMs on five streams.
+static int32_t split_init(ctg_ctx* ctx) {
+  if (ctx->split_start) return CTG_OK;
+  for (int i = 0; i < ctg_ctx::kSplit; i++) {
+    CTG_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->split_st[i], cudaStreamNonBlocking));
+    CTG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->split_done[i], cudaEventDisableTiming));
+  }
+  CTG_CUDA(ctx, cudaMalloc(&ctx->split_part, ctg_ctx::kSplit * sizeof(G2XYZZ)));
+  CTG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->split_start, cudaEventDisableTiming));
+  return CTG_OK;
+}
+static void split_destroy(ctg_ctx* ctx) {
+  for (int i = 0; i < ctg_ctx::kSplit; i++) {
+    if (ctx->split_st[i]) { cudaStreamSynchronize(ctx->split_st[i]); cudaStreamDestroy(ctx->split_st[i]); }
+    if (ctx->split_done[i]) cudaEventDestroy(ctx->split_done[i]);
+    msm_ws_free(ctx->split_ws[i]);
+  }
+  if (ctx->split_start) cudaEventDestroy(ctx->split_start);
+  if (ctx->split_part) cudaFree(ctx->split_part);
+}
+static int split_parts(ctg_ctx* ctx, uint64_t n, uint32_t flags, bool from_host) {
+  if (flags & CTG_MSM_TIMED) return 1;   // stage timings are only meaningful for the serial schedule
+  if (ctx->msm_split >= 1) return n >= (uint64_t)ctx->msm_split ? ctx->msm_split : 1;
+  // measured on B200 at 2^22 (tools/split_sweep.py): every extra part costs ~0.9 ms (a second bucket reduction and fix-up that only
+  // partly hide under the other part's accumulate kernel); two parts pay when there is an upload to hide, none otherwise
+  if (n < (1ull << 21) || !from_host) return 1;
+  return 2;
+}
+// d_scalars: device buffer of n scalars; when host_scalars != nullptr it is filled from there first (part by part).
+template <class XY>
+static int32_t msm_any(ctg_ctx* ctx, const ctg_bases* bases, int group, void* d_scalars, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, XY* d_out) {
+  const bool mont = (flags & CTG_SCALARS_MONT) != 0;
+  const int parts = split_parts(ctx, n, flags, host_scalars != nullptr);
+  auto run = [&](MsmWorkspace& ws, const Bases& b, const uint32_t* sc, uint64_t cnt, void* out, cudaStream_t st, float* tm) -> int32_t {
+    return group == 1 ? msm_g1_run(ctx, ws, b, sc, cnt, mont, (G1XYZZ*)out, st, tm) : msm_g2_run(ctx, ws, b, sc, cnt, mont, (G2XYZZ*)out, st, tm);
+  };
+  if (parts <= 1) {
+    if (host_scalars && n) CTG_CUDA(ctx, cudaMemcpyAsync(d_scalars, host_scalars, n * sizeof(Fr), cudaMemcpyHostToDevice, ctx->stream));
+    float tm[3];
+    const bool timed = (flags & CTG_MSM_TIMED) != 0;
+    int32_t rc = run(ctx->ws[0], bases->b, (const uint32_t*)d_scalars, n, d_out, ctx->stream, timed ? tm : nullptr);
+    if (rc == CTG_OK && timed) { g_last_timings.msm_sort_ms = tm[0]; g_last_timings.msm_accumulate_ms = tm[1]; g_last_timings.msm_reduce_ms = tm[2]; }
+    return rc;
+  }
+  CTG_TRY(split_init(ctx));
+  CTG_CUDA(ctx, cudaEventRecord(ctx->split_start, ctx->stream));
+  const size_t pb = group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+  const uint64_t stride = bases->b.stride ? bases->b.stride : bases->b.n;
+  for (int p = 0; p < parts; p++) {
+    const uint64_t lo = n * (uint64_t)p / parts, hi = n * (uint64_t)(p + 1) / parts, cnt = hi - lo;
+    cudaStream_t st = ctx->split_st[p];
+    CTG_CUDA(ctx, cudaStreamWaitEvent(st, ctx->split_start, 0));
+    Fr* sc = (Fr*)d_scalars + lo;
+    if (host_scalars && cnt) CTG_CUDA(ctx, cudaMemcpyAsync(sc, (const Fr*)host_scalars + lo, cnt * sizeof(Fr), cudaMemcpyHostToDevice, st));
+    Bases view = bases->b;
+    view.pts = (char*)bases->b.pts + lo * pb;
+    view.n = cnt;
+    view.stride = stride;
+    CTG_TRY(run(ctx->split_ws[p], view, (const uint32_t*)sc, cnt, (XY*)ctx->split_part + p, st, nullptr));
+    CTG_CUDA(ctx, cudaEventRecord(ctx->split_done[p], st));
+    CTG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->split_done[p], 0));
+  }
+  if (group == 1) return g1_combine_dev(ctx, (const G1XYZZ*)ctx->split_part, (uint32_t)parts, nullptr, (G1XYZZ*)d_out, ctx->stream);
+  return g2_combine_dev(ctx, (const G2XYZZ*)ctx->split_part, (uint32_t)parts, nullptr, (G2XYZZ*)d_out, ctx->stream);
+}
+
 template <class XY, class AF>
 static int32_t msm_host(ctg_ctx* ctx, const ctg_bases* bases, int group, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, void* out_affine,
                         void* out_xyzz) {
@@ -76,9 +146,7 @@ static int32_t msm_host(ctg_ctx* ctx, const ctg_bases* bases, int group, const c
   char* d = (char*)ctx->scratch;
   XY* d_res = (XY*)(d + ((sb + 63) & ~(size_t)63));
   AF* d_aff = (AF*)(d_res + 1);
-  if (n) CTG_CUDA(ctx, cudaMemcpyAsync(d, host_scalars, sb, cudaMemcpyHostToDevice, ctx->stream));
-  if (group == 1) CTG_TRY(ctg_msm_g1_dev(ctx, bases, d, n, flags, d_res));
-  else CTG_TRY(ctg_msm_g2_dev(ctx, bases, d, n, flags, d_res));
+  CTG_TRY(msm_any<XY>(ctx, bases, group, d, host_scalars, n, flags, d_res));
   if (out_xyzz) CTG_CUDA(ctx, cudaMemcpyAsync(out_xyzz, d_res, sizeof(XY), cudaMemcpyDeviceToHost, ctx->stream));
   if (out_affine) {
     if (group == 1) CTG_TRY(g1_to_affine_dev(ctx, (const G1XYZZ*)d_res, (G1Affine*)d_aff, 1, ctx->stream));
@@ -120,6 +188,7 @@ void ctg_ctx_destroy(ctg_ctx* ctx) {
   }
   lanes_destroy(ctx);
   for (auto& w : ctx->ws) msm_ws_free(w);
+  split_destroy(ctx);
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->events_ready) for (auto& e : ctx->ev) cudaEventDestroy(e);
@@ -287,6 +356,12 @@ int32_t ctg_ctx_set_ba_levels(ctg_ctx* ctx, int levels) {
   ctx->ba_levels = levels;
   return CTG_OK;
 }
+int32_t ctg_ctx_set_msm_split(ctg_ctx* ctx, int parts) {
+  if (!ctx) return CTG_ERR_INVALID;
+  if (parts != -1 && (parts < 1 || parts > ctg_ctx::kSplit)) return fail(ctx, CTG_ERR_INVALID, "msm_split must be -1 or in [1, 4]");
+  ctx->msm_split = parts;
+  return CTG_OK;
+}
 int32_t ctg_bases_plan(const ctg_bases* bases, ctg_msm_plan* out) {
   if (!bases || !out) return CTG_ERR_INVALID;
   const MsmPlan& p = bases->b.plan;
@@ -297,19 +372,11 @@ int32_t ctg_bases_plan(const ctg_bases* bases, ctg_msm_plan* out) {
 // ---- MSM --------------------------------------------------------------------------------------
 int32_t ctg_msm_g1_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {
   CTG_TRY(msm_check(ctx, bases, 1, n));
-  float st[3];
-  int32_t rc = msm_g1_run(ctx, ctx->ws[0], bases->b, (const uint32_t*)d_scalars, n, (flags & CTG_SCALARS_MONT) != 0, (G1XYZZ*)d_out_xyzz, ctx->stream,
-                          (flags & 0x100u) ? st : nullptr);
-  if (rc == CTG_OK && (flags & 0x100u)) { g_last_timings.msm_sort_ms = st[0]; g_last_timings.msm_accumulate_ms = st[1]; g_last_timings.msm_reduce_ms = st[2]; }
-  return rc;
+  return msm_any<G1XYZZ>(ctx, bases, 1, const_cast<void*>(d_scalars), nullptr, n, flags, (G1XYZZ*)d_out_xyzz);
 }
 int32_t ctg_msm_g2_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {
   CTG_TRY(msm_check(ctx, bases, 2, n));
-  float st[3];
-  int32_t rc = msm_g2_run(ctx, ctx->ws[0], bases->b, (const uint32_t*)d_scalars, n, (flags & CTG_SCALARS_MONT) != 0, (G2XYZZ*)d_out_xyzz, ctx->stream,
-                          (flags & 0x100u) ? st : nullptr);
-  if (rc == CTG_OK && (flags & 0x100u)) { g_last_timings.msm_sort_ms = st[0]; g_last_timings.msm_accumulate_ms = st[1]; g_last_timings.msm_reduce_ms = st[2]; }
-  return rc;
+  return msm_any<G2XYZZ>(ctx, bases, 2, const_cast<void*>(d_scalars), nullptr, n, flags, (G2XYZZ*)d_out_xyzz);
 }
 
 int32_t ctg_msm_g1(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_affine* out) {
@@ -327,6 +394,29 @@ int32_t ctg_msm_g1_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* h
 int32_t ctg_msm_g2_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g2_xyzz* out) {
   if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
   return msm_host<G2XYZZ, G2Affine>(ctx, bases, 2, host_scalars, n, flags, nullptr, out);
+}
+
+int32_t ctg_host_alloc(ctg_ctx* ctx, size_t bytes, void** h_out) {
+  if (!ctx || !h_out) return CTG_ERR_INVALID;
+  *h_out = nullptr;
+  if (cudaMallocHost(h_out, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return fail(ctx, CTG_ERR_OOM, "host_alloc: cudaMallocHost failed"); }
+  return CTG_OK;
+}
+int32_t ctg_host_free(ctg_ctx* ctx, void* h_ptr) {
+  if (!ctx) return CTG_ERR_INVALID;
+  if (h_ptr) CTG_CUDA(ctx, cudaFreeHost(h_ptr));
+  return CTG_OK;
+}
+int32_t ctg_prepare_inputs(ctg_ctx* ctx, const ctg_bases* gamma_abc_g1, const ctg_fr* public_inputs, uint64_t n_inputs, ctg_g1_affine* out) {
+  if (!ctx || !gamma_abc_g1 || !out || (n_inputs && !public_inputs)) return ctx ? fail(ctx, CTG_ERR_INVALID, "prepare_inputs: null argument") : CTG_ERR_INVALID;
+  if (gamma_abc_g1->b.group != 1 || gamma_abc_g1->b.n != n_inputs + 1)
+    return fail(ctx, CTG_ERR_INVALID, "prepare_inputs: gamma_abc_g1 must hold exactly n_inputs + 1 G1 points (malformed verifying key)");
+  // scalars 1 || public_inputs select gamma_abc_g1[0] and weigh the rest: one MSM over the whole table
+  CTG_TRY(ensure_pinned(ctx, (n_inputs + 1) * sizeof(Fr)));
+  Fr* h = (Fr*)ctx->pinned;
+  h[0] = Fr::one();
+  if (n_inputs) memcpy(h + 1, public_inputs, n_inputs * sizeof(Fr));
+  return msm_host<G1XYZZ, G1Affine>(ctx, gamma_abc_g1, 1, (const ctg_fr*)h, n_inputs + 1, CTG_SCALARS_MONT, out, nullptr);
 }
 
 int32_t ctg_g1_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine) {

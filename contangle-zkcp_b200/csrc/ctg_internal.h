@@ -57,6 +57,7 @@ struct Bases {  // device-resident base table (a proving-key query or a standalo
   uint64_t n;       // points per copy
   MsmPlan plan;
   void* pts;        // [copies][n] affine
+  uint64_t stride = 0;  // distance between copies in points; 0 = n (a point-range view of a larger table sets it to the parent's n)
 };
 
 }  // namespace ctg
@@ -85,6 +86,14 @@ struct ctg_ctx {
   int ba_levels = -1;   // batched-affine tree levels per MSM: -1 = chosen per call (msm.cuh ba_num_levels), 0..6 forced
   std::map<int, ctg::NttDomain> domains;
   ctg::MsmWorkspace ws[2];
+  // split MSM (abi.cu msm_split): point-range parts of one large MSM on their own streams, so that one part's scalar upload,
+  // bucket sort and latency-bound reduction overlap another part's accumulate kernel
+  static constexpr int kSplit = 4;
+  cudaStream_t split_st[kSplit] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t split_done[kSplit] = {nullptr, nullptr, nullptr, nullptr}, split_start = nullptr;
+  ctg::MsmWorkspace split_ws[kSplit];
+  void* split_part = nullptr;   // kSplit XYZZ<Fq2> partial sums
+  int msm_split = -1;           // parts per large MSM: -1 = automatic, 1 = never split
   ctg::ProveLane lanes[ctg::kMaxLanes];
   void* pinned_proofs = nullptr; size_t pinned_proofs_bytes = 0;
   void* scratch = nullptr; size_t scratch_bytes = 0;     // general device scratch (staging)

@@ -534,7 +534,8 @@ template <class F> struct MsmHost {
                      cudaStream_t st, float* stage_ms) {
     const MsmPlan& plan = bases.plan;
     if (n > bases.n) return fail(ctx, CTG_ERR_INVALID, "msm: more scalars than bases");
-    if ((uint64_t)bases.n * plan.copies >= (1ull << 31)) return fail(ctx, CTG_ERR_INVALID, "msm: n * copies must be < 2^31");
+    const uint64_t cstride = bases.stride ? bases.stride : bases.n;
+    if (cstride * plan.copies >= (1ull << 31)) return fail(ctx, CTG_ERR_INVALID, "msm: n * copies must be < 2^31");
     if ((uint64_t)n * plan.nwin >= (1ull << 32)) return fail(ctx, CTG_ERR_INVALID, "msm: n * windows must be < 2^32");
     if (n == 0) {
       CTG_CUDA(ctx, cudaMemsetAsync(d_out, 0, sizeof(XYZZ<F>), st));
@@ -576,7 +577,7 @@ template <class F> struct MsmHost {
     CTG_KERNEL_CHECK(ctx);
     msm_scan_apply_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, ws.cursor, nb, ws.tile_sums, ntiles);
     CTG_KERNEL_CHECK(ctx);
-    msm_scatter_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, bases.n, mont ? 1 : 0, plan, ws.cursor, ws.entries);
+    msm_scatter_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, cstride, mont ? 1 : 0, plan, ws.cursor, ws.entries);
     CTG_KERNEL_CHECK(ctx);
     if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
 

@@ -25,7 +25,7 @@ OP_MUL, OP_ADD, OP_SUB, OP_INV = 0, 1, 2, 3
 
 # every symbol include/ctg_groth16.h declares (checked by tests/test_abi_cpu.py)
 EXPORTS = [
-    "ctg_ctx_create", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_ctx_set_ba_levels", "ctg_sync", "ctg_launch_count",
+    "ctg_ctx_create", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_ctx_set_ba_levels", "ctg_ctx_set_msm_split", "ctg_sync", "ctg_launch_count",
     "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch",
     "ctg_fr_mul_batch", "ctg_fq_mul_batch", "ctg_imad_peak_probe", "ctg_ntt_fr", "ctg_ntt_fr_dev",
     "ctg_bases_upload_g1", "ctg_bases_upload_g2", "ctg_bases_progression_g1", "ctg_bases_progression_g2",
@@ -33,7 +33,7 @@ EXPORTS = [
     "ctg_msm_g2_dev", "ctg_msm_g1_partial", "ctg_msm_g2_partial", "ctg_g1_combine", "ctg_g2_combine",
     "ctg_g1_combine_dev", "ctg_g2_combine_dev", "ctg_pk_upload", "ctg_pk_free", "ctg_r1cs_upload",
     "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch", "ctg_pk_upload_shard", "ctg_prove_partial",
-    "ctg_prove_combine",
+    "ctg_prove_combine", "ctg_prepare_inputs", "ctg_host_alloc", "ctg_host_free",
 ]
 
 
@@ -163,6 +163,10 @@ class Context:
         """MSM bucket accumulation: number of batched-affine tree levels (-1 = automatic, 0 = XYZZ only)."""
         self._check(load().ctg_ctx_set_ba_levels(self.h, int(levels)))
 
+    def set_msm_split(self, parts=-1):
+        """Point-range parts per stand-alone MSM (-1 = automatic, 1 = never split)."""
+        self._check(load().ctg_ctx_set_msm_split(self.h, int(parts)))
+
     def field_op(self, field, op, a, b):
         w = {FIELD_FR: FR_W, FIELD_FQ: FQ_W, FIELD_FQ2: 2 * FQ_W}[field]
         a, b = _arr(a, w), _arr(b, w)
@@ -239,6 +243,31 @@ class Context:
         flags = (SCALARS_MONT if mont else 0) | (MSM_TIMED if timed else 0)
         fn = load().ctg_msm_g1_dev if bases.group == 1 else load().ctg_msm_g2_dev
         self._check(fn(self.h, bases.handle, C.c_void_p(d_scalars), C.c_uint64(n), C.c_uint32(flags), C.c_void_p(d_out_xyzz)))
+
+    def pinned_like(self, arr):
+        """Copy of `arr` (uint32 words) in page-locked host memory (ctg_host_alloc); keep the returned array alive while in use.
+        Free with ctx.pinned_free(a)."""
+        arr = np.ascontiguousarray(arr, dtype=np.uint32)
+        p = C.c_void_p()
+        self._check(load().ctg_host_alloc(self.h, C.c_size_t(arr.nbytes), C.byref(p)))
+        buf = (C.c_uint32 * arr.size).from_address(p.value)
+        out = np.frombuffer(buf, dtype=np.uint32).reshape(arr.shape)
+        out[...] = arr
+        self._pinned = getattr(self, "_pinned", {})
+        self._pinned[out.ctypes.data] = p.value
+        return out
+
+    def pinned_free(self, a):
+        p = getattr(self, "_pinned", {}).pop(a.ctypes.data, None)
+        if p is not None:
+            self._check(load().ctg_host_free(self.h, C.c_void_p(p)))
+
+    def prepare_inputs(self, gamma_abc: Bases, public_inputs_mont):
+        """ark_groth16::prepare_inputs: gamma_abc_g1[0] + sum_i x_i * gamma_abc_g1[i + 1] (affine, (24,) uint32)."""
+        x = _arr(public_inputs_mont, FR_W) if len(public_inputs_mont) else np.zeros((0, FR_W), dtype=np.uint32)
+        out = np.zeros(G1_W, dtype=np.uint32)
+        self._check(load().ctg_prepare_inputs(self.h, gamma_abc.handle, _ptr(x), C.c_uint64(x.shape[0]), _ptr(out)))
+        return out
 
     def msm_partial(self, bases: Bases, scalars, mont=False):
         scalars = _arr(scalars, FR_W)

@@ -112,6 +112,10 @@ int32_t ctg_sync(ctg_ctx* ctx);
  * binary-GCD inversion per 64 additions) before the XYZZ accumulation (8M + 2S).  -1 (default) = chosen per call from the
  * size; 0 = XYZZ only; 1..6 forced (tests, sweeps).  The result is the same group element either way. */
 int32_t ctg_ctx_set_ba_levels(ctg_ctx* ctx, int levels);
+/* Large stand-alone MSMs (ctg_msm_*) are cut into `parts` point ranges that run as complete MSMs on their own streams, so that
+ * one part's scalar upload, bucket sort and reduction overlap another part's accumulate kernel; the partial sums are added on
+ * the device.  -1 (default) = automatic (2 for host scalars from 2^21 points up, else 1), 1 = never, up to 4. */
+int32_t ctg_ctx_set_msm_split(ctg_ctx* ctx, int parts);
 uint64_t ctg_launch_count(ctg_ctx* ctx); /* kernels launched by this context so far */
 int32_t ctg_last_timings(ctg_ctx* ctx, ctg_timings* out);
 
@@ -120,6 +124,10 @@ int32_t ctg_dev_alloc(ctg_ctx* ctx, size_t bytes, void** d_out);
 int32_t ctg_dev_free(ctg_ctx* ctx, void* d_ptr);
 int32_t ctg_h2d(ctg_ctx* ctx, void* d_dst, const void* h_src, size_t bytes);
 int32_t ctg_d2h(ctg_ctx* ctx, void* h_dst, const void* d_src, size_t bytes);
+/* Page-locked host memory for assignments and scalars: host -> device copies from it run at full PCIe rate and asynchronously
+ * (the Rust shim packs z = instance ++ witness straight into such a buffer).  Pageable buffers are accepted everywhere, slower. */
+int32_t ctg_host_alloc(ctg_ctx* ctx, size_t bytes, void** h_out);
+int32_t ctg_host_free(ctg_ctx* ctx, void* h_ptr);
 
 /* ---- field kernels (replaces ark-ff Fp256/Fp384 mul_assign/add_assign/sub_assign; used by
  *      tests and the ncu integer-pipe captures) --------------------------------------- */
@@ -172,6 +180,13 @@ int32_t ctg_g1_combine(ctg_ctx* ctx, const ctg_g1_xyzz* host_partials, uint32_t 
 int32_t ctg_g2_combine(ctg_ctx* ctx, const ctg_g2_xyzz* host_partials, uint32_t k, ctg_g2_affine* out);
 int32_t ctg_g1_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine);
 int32_t ctg_g2_combine_dev(ctg_ctx* ctx, const void* d_partials, uint32_t k, void* d_out_affine);
+
+/* ---- verifier side of the same MSM ---------------------------------------------
+ * ark_groth16::prepare_inputs(pvk, public_inputs): gamma_abc_g1[0] + sum_i public_inputs[i] * gamma_abc_g1[i + 1], the only
+ * size-dependent step of Groth16::verify (lib/src/zk/encryption.rs:152, lib/src/zk/sample_entries.rs:126: n + 2 public inputs
+ * for an n-chunk ciphertext, circuits-ark/src/encryption.rs:139-152).  gamma_abc_g1: a base table of exactly n_inputs + 1 points
+ * (CTG_ERR_INVALID otherwise, arkworks' SynthesisError::MalformedVerifyingKey); public_inputs: Montgomery Fr images. */
+int32_t ctg_prepare_inputs(ctg_ctx* ctx, const ctg_bases* gamma_abc_g1, const ctg_fr* public_inputs, uint64_t n_inputs, ctg_g1_affine* out);
 
 /* ---- proving key / R1CS caches and the prover ---------------------------------------- */
 /* copies / c_bits as for ctg_bases_upload_* (applied to every query). */

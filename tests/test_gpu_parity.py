@@ -220,6 +220,46 @@ def test_msm_g2_batched_affine_levels(ctx, levels, kind):
         ctx.set_ba_levels(-1)
 
 
+@pytest.mark.parametrize("n_inputs", [0, 1, 5, 2050])
+def test_prepare_inputs_matches_arkworks_loop(ctx, n_inputs):
+    """ark_groth16::prepare_inputs: g_ic = gamma_abc[0]; g_ic += gamma_abc[i + 1] * x_i -- against that loop in the oracle."""
+    gamma = _g1_bases(n_inputs + 1, 1234)
+    if n_inputs > 3:
+        gamma[2] = 0
+    xs = ark.random_scalars_canon(n_inputs, 77, "poe") if n_inputs else np.zeros((0, 8), dtype=np.uint32)
+    t = ctx.bases_g1(gamma)
+    got = ctx.prepare_inputs(t, ark.fr_to_mont(xs) if n_inputs else xs)
+    want = gamma[0] if n_inputs == 0 else ark.g1_add(gamma[0], ark.msm_g1(gamma[1:], xs))
+    assert np.array_equal(got, want)
+    with pytest.raises(ctg.CtgError):
+        ctx.prepare_inputs(t, np.zeros((n_inputs + 1, 8), dtype=np.uint32))     # malformed verifying key
+    t.free()
+
+
+@pytest.mark.parametrize("parts", [2, 3, 4])
+def test_msm_split_parts_match(ctx, parts):
+    """Point-range parts on separate streams + on-device combine give the same point (G1 with precomputed copies, G2)."""
+    n = 5003
+    pts = _g1_bases(n, 17)
+    sc = ark.random_scalars_canon(n, 18, "poe")
+    want = ark.msm_g1(pts, sc)
+    p2 = ark.g2_progression(ark.g2_generator(), fm(3), fm(5), 600)
+    sc2 = ark.random_scalars_canon(600, 19, "uniform")
+    want2 = ark.msm_g2(p2, sc2)
+    ctx.set_msm_split(parts)
+    try:
+        for copies, c_bits in ((1, 0), (4, 8)):
+            t = ctx.bases_g1(pts, copies=copies, c_bits=c_bits)
+            assert np.array_equal(ctx.msm(t, sc), want)
+            assert np.array_equal(ctx.msm(t, sc[:777]), ark.msm_g1(pts[:777], sc[:777]))
+            t.free()
+        t2 = ctx.bases_g2(p2, copies=2, c_bits=6)
+        assert np.array_equal(ctx.msm(t2, sc2), want2)
+        t2.free()
+    finally:
+        ctx.set_msm_split(-1)
+
+
 def test_msm_g1_prefix_and_errors(ctx):
     n = 2000
     pts = _g1_bases(n, 3)
