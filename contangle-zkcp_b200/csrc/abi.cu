@@ -312,12 +312,12 @@ static int32_t bases_finish(ctg_ctx* ctx, ctg_bases* h) {
 }
 int32_t ctg_bases_upload_g1(ctg_ctx* ctx, const ctg_g1_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
   CTG_TRY(bases_new(ctx, 1, n, copies, c_bits, out));
-  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G1Affine), cudaMemcpyHostToDevice, ctx->stream));
+  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G1Affine), cudaMemcpyDefault, ctx->stream));
   return bases_finish(ctx, *out);
 }
 int32_t ctg_bases_upload_g2(ctg_ctx* ctx, const ctg_g2_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
   CTG_TRY(bases_new(ctx, 2, n, copies, c_bits, out));
-  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G2Affine), cudaMemcpyHostToDevice, ctx->stream));
+  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G2Affine), cudaMemcpyDefault, ctx->stream));
   return bases_finish(ctx, *out);
 }
 int32_t ctg_bases_progression_g1(ctg_ctx* ctx, const ctg_g1_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {

@@ -141,6 +141,10 @@ int32_t ntt_run(ctg_ctx* ctx, Fr* d_data, int log_n, int inverse, int coset, cud
 int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);      // natural in, natural out
 int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);        // natural in, bit-reversed out
 
+int32_t fr_pow_table(ctg_ctx* ctx, Fr* d_out, uint64_t n, const Fr& base, const Fr& scale, cudaStream_t st);  // out[i] = scale * base^i
+Fr fr_root_of_unity(int log_n);   // generator of the 2^log_n domain (ark-poly Radix2EvaluationDomain::group_gen), Montgomery
+Fr fr_from_u64(uint64_t x);
+
 // msm_g1.cu / msm_g2.cu
 MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes);
 int32_t msm_g1_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,

@@ -254,6 +254,11 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
   return CTG_OK;
 }
 
+// exported for setup.cu (key generation): power tables and the domain generator
+int32_t fr_pow_table(ctg_ctx* ctx, Fr* d_out, uint64_t n, const Fr& base, const Fr& scale, cudaStream_t st) { return fill_pow_table(ctx, d_out, n, base, scale, st); }
+Fr fr_root_of_unity(int log_n) { return host_root_of_unity(log_n); }
+Fr fr_from_u64(uint64_t x) { return host_fr_from_u64(x); }
+
 struct PassGeom { int log_blk, S; };
 // DIF order (large sub-transforms first).  DIT uses the same list reversed.
 static std::vector<PassGeom> plan_passes(int log_n) {

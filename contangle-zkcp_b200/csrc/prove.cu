@@ -158,13 +158,13 @@ static cudaError_t upload_ext_range(A* dst, const A* query, uint64_t m, const A*
   const uint64_t hi = lo + cnt;
   if (lo < m) {
     const uint64_t q_hi = hi < m ? hi : m;
-    cudaError_t e = cudaMemcpyAsync(dst, query + lo, (q_hi - lo) * sizeof(A), cudaMemcpyHostToDevice, st);
+    cudaError_t e = cudaMemcpyAsync(dst, query + lo, (q_hi - lo) * sizeof(A), cudaMemcpyDefault, st);
     if (e != cudaSuccess) return e;
   }
   for (int k = 0; k < 3; k++) {
     const uint64_t pos = m + k;
     if (pos >= lo && pos < hi && extras[k]) {
-      cudaError_t e = cudaMemcpyAsync(dst + (pos - lo), extras[k], sizeof(A), cudaMemcpyHostToDevice, st);
+      cudaError_t e = cudaMemcpyAsync(dst + (pos - lo), extras[k], sizeof(A), cudaMemcpyDefault, st);
       if (e != cudaSuccess) return e;
     }
   }
@@ -210,16 +210,16 @@ int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, 
   PK_CUDA(upload_ext_range((G1Affine*)pk->a_ext.pts, (const G1Affine*)v->a_query, m, a_extra, pk->ext_lo, pk->ext_cnt, st));
   PK_CUDA(upload_ext_range((G1Affine*)pk->b1_ext.pts, (const G1Affine*)v->b_g1_query, m, b1_extra, pk->ext_lo, pk->ext_cnt, st));
   PK_CUDA(upload_ext_range((G2Affine*)pk->b2_ext.pts, (const G2Affine*)v->b_g2_query, m, b2_extra, pk->ext_lo, pk->ext_cnt, st));
-  if (pk->l_cnt) PK_CUDA(cudaMemcpyAsync(pk->l.pts, (const G1Affine*)v->l_query + pk->l_lo, pk->l_cnt * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+  if (pk->l_cnt) PK_CUDA(cudaMemcpyAsync(pk->l.pts, (const G1Affine*)v->l_query + pk->l_lo, pk->l_cnt * sizeof(G1Affine), cudaMemcpyDefault, st));
   // h_query: stage natural order in scratch, gather this shard's bit-reversed positions; position n-1 holds delta_g1
   if (n > 1 && pk->h_cnt) {
     if ((rc = ensure_scratch(ctx, (n - 1) * sizeof(G1Affine))) != CTG_OK) return cleanup(rc);
-    PK_CUDA(cudaMemcpyAsync(ctx->scratch, v->h_query, (n - 1) * sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+    PK_CUDA(cudaMemcpyAsync(ctx->scratch, v->h_query, (n - 1) * sizeof(G1Affine), cudaMemcpyDefault, st));
     bitrev_gather_g1_kernel<<<(unsigned)((pk->h_cnt + 255) / 256), 256, 0, st>>>((const G1Affine*)ctx->scratch, (G1Affine*)pk->h_ext.pts, n - 1, log_n, pk->h_lo, pk->h_cnt);
     ctx->launches++;
   }
   if (n - 1 >= pk->h_lo && n - 1 < pk->h_lo + pk->h_cnt)
-    PK_CUDA(cudaMemcpyAsync((G1Affine*)pk->h_ext.pts + (n - 1 - pk->h_lo), v->delta_g1, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+    PK_CUDA(cudaMemcpyAsync((G1Affine*)pk->h_ext.pts + (n - 1 - pk->h_lo), v->delta_g1, sizeof(G1Affine), cudaMemcpyDefault, st));
   for (Bases* b : {&pk->a_ext, &pk->b1_ext, &pk->b2_ext, &pk->l, &pk->h_ext})
     if ((rc = finish_bases(ctx, *b)) != CTG_OK) return cleanup(rc);
   PK_CUDA(cudaStreamSynchronize(st));

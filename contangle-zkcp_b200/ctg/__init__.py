@@ -34,6 +34,7 @@ EXPORTS = [
     "ctg_g1_combine_dev", "ctg_g2_combine_dev", "ctg_pk_upload", "ctg_pk_free", "ctg_r1cs_upload",
     "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch", "ctg_pk_upload_shard", "ctg_prove_partial",
     "ctg_prove_combine", "ctg_prepare_inputs", "ctg_host_alloc", "ctg_host_free",
+    "ctg_generate_parameters", "ctg_params_pk_view", "ctg_params_download", "ctg_params_free",
 ]
 
 
@@ -49,6 +50,18 @@ class PkView(C.Structure):
                 ("b_g2_query", C.c_void_p), ("b_g2_len", C.c_uint64),
                 ("h_query", C.c_void_p), ("h_len", C.c_uint64),
                 ("l_query", C.c_void_p), ("l_len", C.c_uint64)]
+
+
+class Trapdoor(C.Structure):
+    _fields_ = [(k, C.c_uint32 * FR_W) for k in ("alpha", "beta", "gamma", "delta", "tau")] + [("g1", C.c_uint32 * G1_W), ("g2", C.c_uint32 * G2_W)]
+
+
+PARAMS_OUT_FIELDS = ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "gamma_g2", "delta_g2", "gamma_abc_g1",
+                     "a_query", "b_g1_query", "b_g2_query", "h_query", "l_query")
+
+
+class ParamsOut(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in PARAMS_OUT_FIELDS]
 
 
 class Csr(C.Structure):
@@ -83,7 +96,7 @@ def load():
         lib.ctg_last_error.restype = C.c_char_p
         lib.ctg_launch_count.restype = C.c_uint64
         lib.ctg_bases_len.restype = C.c_uint64
-        for name in ("ctg_ctx_destroy", "ctg_bases_free", "ctg_pk_free", "ctg_r1cs_free"):
+        for name in ("ctg_ctx_destroy", "ctg_bases_free", "ctg_pk_free", "ctg_r1cs_free", "ctg_params_free"):
             getattr(lib, name).restype = None
         _lib = lib
     return _lib
@@ -307,7 +320,8 @@ class Context:
                                                    int(shard[0]), int(shard[1]), C.byref(h)))
         return DevicePk(self, h, pk["a_query"].shape[0])
 
-    def upload_r1cs(self, r1cs: dict):
+    @staticmethod
+    def _csr_triplet(r1cs):
         mats, keep = [], []
         for k in "abc":
             m = r1cs[k]
@@ -316,6 +330,27 @@ class Context:
             val = _arr(m["val"]).reshape(-1, FR_W)
             keep += [rp, col, val]
             mats.append(Csr(rp.ctypes.data, col.ctypes.data, val.ctypes.data))
+        return mats, keep
+
+    def generate_parameters(self, r1cs: dict, trapdoor: dict):
+        """ark_groth16::generate_parameters on the device.  trapdoor: Montgomery Fr word arrays alpha, beta, gamma, delta, tau
+        and affine generators g1 (24 words), g2 (48 words).  Returns DeviceParams (key resident in HBM)."""
+        mats, keep = self._csr_triplet(r1cs)
+        td = Trapdoor()
+        for k, w in (("alpha", FR_W), ("beta", FR_W), ("gamma", FR_W), ("delta", FR_W), ("tau", FR_W), ("g1", G1_W), ("g2", G2_W)):
+            a = _arr(trapdoor[k]).reshape(w)
+            getattr(td, k)[:] = [int(x) for x in a]
+        h = C.c_void_p()
+        self._check(load().ctg_generate_parameters(self.h, C.c_uint64(r1cs["num_instance"]), C.c_uint64(r1cs["num_witness"]),
+                                                   C.c_uint64(r1cs["num_constraints"]), C.byref(mats[0]), C.byref(mats[1]), C.byref(mats[2]),
+                                                   C.byref(td), C.byref(h)))
+        n = 1
+        while n < r1cs["num_instance"] + r1cs["num_constraints"]:
+            n *= 2
+        return DeviceParams(self, h, r1cs["num_instance"], r1cs["num_witness"], r1cs["num_constraints"], n)
+
+    def upload_r1cs(self, r1cs: dict):
+        mats, keep = self._csr_triplet(r1cs)
         h = C.c_void_p()
         self._check(load().ctg_r1cs_upload(self.h, C.c_uint64(r1cs["num_instance"]), C.c_uint64(r1cs["num_witness"]),
                                            C.c_uint64(r1cs["num_constraints"]), C.byref(mats[0]), C.byref(mats[1]), C.byref(mats[2]), C.byref(h)))
@@ -396,4 +431,55 @@ class DeviceR1cs:
     def free(self):
         if self.handle:
             load().ctg_r1cs_free(self.ctx.h, self.handle)
+            self.handle = None
+
+
+class DeviceParams:
+    """Output of Context.generate_parameters: ark_groth16::ProvingKey (+ VerifyingKey) in HBM."""
+
+    def __init__(self, ctx, handle, ni, nw, nc, n):
+        self.ctx, self.handle, self.ni, self.nw, self.nc, self.n = ctx, handle, ni, nw, nc, n
+
+    def _view(self):
+        v, gp, gl = PkView(), C.c_void_p(), C.c_uint64()
+        self.ctx._check(load().ctg_params_pk_view(self.ctx.h, self.handle, C.byref(v), C.byref(gp), C.byref(gl)))
+        return v, gp, int(gl.value)
+
+    def to_device_pk(self, copies=0, c_bits=0, shard=None):
+        """Device-to-device: build the prover's key cache (ctg_pk) straight from the generated key."""
+        v, _, _ = self._view()
+        h = C.c_void_p()
+        if shard is None:
+            self.ctx._check(load().ctg_pk_upload(self.ctx.h, C.byref(v), C.c_uint64(self.ni), C.c_uint64(self.nc), copies, c_bits, C.byref(h)))
+        else:
+            self.ctx._check(load().ctg_pk_upload_shard(self.ctx.h, C.byref(v), C.c_uint64(self.ni), C.c_uint64(self.nc), copies, c_bits,
+                                                       int(shard[0]), int(shard[1]), C.byref(h)))
+        return DevicePk(self.ctx, h, self.ni + self.nw)
+
+    def gamma_abc_bases(self, copies=1, c_bits=0):
+        """vk.gamma_abc_g1 as a base table for Context.prepare_inputs (device-to-device)."""
+        _, gp, gl = self._view()
+        h = C.c_void_p()
+        self.ctx._check(load().ctg_bases_upload_g1(self.ctx.h, gp, C.c_uint64(gl), copies, c_bits, C.byref(h)))
+        return Bases(self.ctx, h, 1)
+
+    def download(self, fields=PARAMS_OUT_FIELDS):
+        """Host copies (dict of uint32 word arrays) of the requested key members."""
+        m, shapes = self.ni + self.nw, {}
+        for k in ("alpha_g1", "beta_g1", "delta_g1"):
+            shapes[k] = (G1_W,)
+        for k in ("beta_g2", "gamma_g2", "delta_g2"):
+            shapes[k] = (G2_W,)
+        shapes.update(gamma_abc_g1=(self.ni, G1_W), a_query=(m, G1_W), b_g1_query=(m, G1_W), b_g2_query=(m, G2_W),
+                      h_query=(self.n - 1, G1_W), l_query=(self.nw, G1_W))
+        out, dst = {}, ParamsOut()
+        for k in fields:
+            out[k] = np.zeros(shapes[k], dtype=np.uint32)
+            setattr(dst, k, out[k].ctypes.data)
+        self.ctx._check(load().ctg_params_download(self.ctx.h, self.handle, C.byref(dst)))
+        return out
+
+    def free(self):
+        if self.handle:
+            load().ctg_params_free(self.ctx.h, self.handle)
             self.handle = None

@@ -152,7 +152,8 @@ int32_t ctg_ntt_fr(ctg_ctx* ctx, ctg_fr* host_data, uint32_t log_n, int inverse,
 int32_t ctg_ntt_fr_dev(ctg_ctx* ctx, void* d_data, uint32_t log_n, int inverse, int coset);
 
 /* ---- base tables and MSM (replaces ark-ec 0.3.0 VariableBaseMSM::multi_scalar_mul) ---- */
-/* copies >= 1: keep 2^(c*G*j) * P for j < copies in HBM so that only G = ceil(W/copies) bucket
+/* host_points may also be a device pointer (unified addressing; e.g. from ctg_params_pk_view).
+ * copies >= 1: keep 2^(c*G*j) * P for j < copies in HBM so that only G = ceil(W/copies) bucket
  * sets are reduced (0 = let the library choose); c_bits = 0 lets the library choose. */
 int32_t ctg_bases_upload_g1(ctg_ctx* ctx, const ctg_g1_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out);
 int32_t ctg_bases_upload_g2(ctg_ctx* ctx, const ctg_g2_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out);
@@ -219,6 +220,34 @@ int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, ui
 int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
                           ctg_proof_partial* out, ctg_timings* timings /* may be NULL */);
 int32_t ctg_prove_combine(ctg_ctx* ctx, const ctg_proof_partial* partials, uint32_t k, const ctg_fr* r, const ctg_fr* s, ctg_proof* out);
+
+/* ---- key generation ---------------------------------------------------------------
+ * ark_groth16::generate_parameters(circuit, alpha, beta, gamma, delta, g1_generator, g2_generator, rng) after synthesis
+ * (the body of Groth16::setup / generate_random_parameters: lib/src/zk/encryption.rs:169, sample_entries.rs:141,
+ * property.rs:192).  The caller draws the trapdoor -- alpha, beta, gamma, delta, the two generators, then
+ * tau = domain.sample_element_outside_domain(rng), in arkworks' order -- and passes it in (Montgomery Fr images, affine
+ * generators); the R1CS is the same to_matrices() triple ctg_r1cs_upload takes.  The key stays in HBM:
+ * ctg_params_pk_view hands DEVICE pointers that ctg_pk_upload / ctg_pk_upload_shard / ctg_bases_upload_g1 accept as they
+ * accept host pointers; ctg_params_download copies any part to caller-owned host buffers (for serialisation).
+ * Errors: CTG_ERR_INVALID if gamma or delta is 0 or tau lies in the evaluation domain (arkworks panics on both). */
+typedef struct { ctg_fr alpha, beta, gamma, delta, tau; ctg_g1_affine g1; ctg_g2_affine g2; } ctg_trapdoor;
+typedef struct ctg_params ctg_params; /* ark_groth16::ProvingKey (with its VerifyingKey) resident in HBM */
+typedef struct {                      /* caller-allocated host buffers; NULL members are skipped */
+  ctg_g1_affine* alpha_g1; ctg_g1_affine* beta_g1; ctg_g1_affine* delta_g1;
+  ctg_g2_affine* beta_g2; ctg_g2_affine* gamma_g2; ctg_g2_affine* delta_g2;
+  ctg_g1_affine* gamma_abc_g1; /* num_instance */
+  ctg_g1_affine* a_query;      /* m */
+  ctg_g1_affine* b_g1_query;   /* m */
+  ctg_g2_affine* b_g2_query;   /* m */
+  ctg_g1_affine* h_query;      /* n - 1 */
+  ctg_g1_affine* l_query;      /* num_witness */
+} ctg_params_out;
+int32_t ctg_generate_parameters(ctg_ctx* ctx, uint64_t num_instance, uint64_t num_witness, uint64_t num_constraints, const ctg_csr* a,
+                                const ctg_csr* b, const ctg_csr* c, const ctg_trapdoor* trapdoor, ctg_params** out);
+int32_t ctg_params_pk_view(ctg_ctx* ctx, const ctg_params* params, ctg_pk_view* out, const ctg_g1_affine** gamma_abc_g1 /* may be NULL */,
+                           uint64_t* gamma_abc_len /* may be NULL */);
+int32_t ctg_params_download(ctg_ctx* ctx, const ctg_params* params, const ctg_params_out* dst);
+void ctg_params_free(ctg_ctx* ctx, ctg_params* params);
 
 #ifdef __cplusplus
 }

@@ -448,3 +448,103 @@ def test_prove_rejects_mismatched_shapes(ctx):
     with pytest.raises(ctg.CtgError):
         ctx.upload_pk(bad, r1a["num_instance"], r1a["num_constraints"])
     dpk.free(); drb.free()
+
+
+# ----------------------------------------------------------------------------- key generation
+KEY_MEMBERS = ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "gamma_g2", "delta_g2", "gamma_abc_g1",
+               "a_query", "b_g1_query", "b_g2_query", "h_query", "l_query")
+
+
+def test_generate_parameters_vs_bigint_oracle(ctx):
+    """Every member of the key against oracle/py generate_parameters (independent big-int restatement)."""
+    cs, _ = G.mul_chain(3, rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD))
+    td = _trapdoor()
+    want = ark.pk_from_py(G.generate_parameters(cs, td))
+    dp = ctx.generate_parameters(ark.r1cs_from_py(cs), util.trapdoor_words(td))
+    got = dp.download()
+    for k in KEY_MEMBERS:
+        assert np.array_equal(got[k].reshape(want[k].shape), want[k]), k
+    dp.free()
+
+
+@pytest.mark.parametrize("shape", ["mulchain10", "mulchain14", "poe100"])
+def test_generate_parameters_vs_oracle(ctx, shape):
+    """Against the arkworks-algorithm C++ restatement (Lagrange coefficients + fixed-base multiplication); poe100 has the
+    heavy constant column (hundreds of rows touch z[0]) and 103 instance columns; mulchain14 takes the 16-bit-window path."""
+    if shape.startswith("mulchain"):
+        r1cs, _, _ = S.mul_chain(int(shape[8:]))
+    else:
+        r1cs, _, _ = S.poe_shape(100)
+    td = _trapdoor()
+    want = util.trapdoor_pk_arrays(util.cs_from_arrays(r1cs), td)
+    dp = ctx.generate_parameters(r1cs, util.trapdoor_words(td))
+    got = dp.download()
+    for k in KEY_MEMBERS:
+        assert np.array_equal(got[k].reshape(want[k].shape), want[k]), k
+    dp.free()
+
+
+@pytest.mark.parametrize("shape", ["mulchain6", "poe1"])
+def test_setup_prove_verify_round_trip(ctx, shape):
+    """The reference's own test shape (circuits-ark/src/encryption.rs:403-411): setup -> prove -> verify accepts, and rejects a
+    wrong public input.  Setup and prove run on the GPU (key never leaves HBM between them); prepare_inputs runs on the GPU
+    and is compared with the oracle's; the pairing equation is the big-int oracle (oracle/py/pairing.py)."""
+    if shape.startswith("mulchain"):
+        r1cs, zm, z = S.mul_chain(int(shape[8:]))
+    else:
+        r1cs, zm, z = S.poe_shape(1, gates=300, bits=64)
+    assert S.r1cs_is_satisfied(r1cs, z)
+    td = _trapdoor()
+    dp = ctx.generate_parameters(r1cs, util.trapdoor_words(td))
+    dpk = dp.to_device_pk()
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    proof = ctx.prove(dpk, dr, zm, fm(r), fm(s))
+    key = dp.download(("alpha_g1", "beta_g2", "gamma_g2", "delta_g2", "gamma_abc_g1"))
+    ni = r1cs["num_instance"]
+    public = z[1:ni]
+    assert util.groth16_verify_words(key, proof, public)
+    bad = list(public); bad[-1] = (bad[-1] + 1) % B.R_MOD
+    assert not util.groth16_verify_words(key, proof, bad)
+    # the proof also equals the trapdoor closed form
+    assert util.proof_to_py(proof) == G.closed_form_proof(util.cs_from_arrays(r1cs), td, z, r, s)
+    # verifier-side aggregation on the device from the device-resident gamma_abc_g1
+    from oracle.py import pairing as PR
+    gb = dp.gamma_abc_bases()
+    acc = ctx.prepare_inputs(gb, ark.fr_mont_from_ints(public))
+    assert ark.g1_to_py(acc)[0] == PR.prepare_inputs(ark.g1_to_py(key["gamma_abc_g1"]), public)
+    gb.free(); dpk.free(); dr.free(); dp.free()
+
+
+def test_generate_parameters_sharded_key_from_device(ctx):
+    """Point-range shards built device-to-device from the generated key give the same proof as the whole key."""
+    r1cs, zm, z = S.mul_chain(9)
+    td = _trapdoor()
+    dp = ctx.generate_parameters(r1cs, util.trapdoor_words(td))
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD))
+    whole = dp.to_device_pk()
+    want = ctx.prove(whole, dr, zm, r, s)
+    parts = []
+    for i in range(3):
+        sh = dp.to_device_pk(shard=(i, 3))
+        parts.append(ctx.prove_partial(sh, dr, zm, r, s))
+        sh.free()
+    got = ctx.prove_combine(np.stack(parts), r, s)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    whole.free(); dr.free(); dp.free()
+
+
+def test_generate_parameters_rejects_bad_trapdoor(ctx):
+    r1cs, _, _ = S.mul_chain(4)
+    td = _trapdoor()
+    for field_name, value in (("delta", 0), ("gamma", 0), ("tau", 1), ("tau", B.fr_root_of_unity(4))):
+        w = util.trapdoor_words(td)
+        w[field_name] = fm(value)
+        with pytest.raises(ctg.CtgError):
+            ctx.generate_parameters(r1cs, w)
+    bad = dict(r1cs)
+    bad["a"] = dict(r1cs["a"]); bad["a"]["col"] = r1cs["a"]["col"].copy(); bad["a"]["col"][0] = 10**6
+    with pytest.raises(ctg.CtgError):
+        ctx.generate_parameters(bad, util.trapdoor_words(td))

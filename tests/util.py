@@ -35,8 +35,10 @@ def trapdoor_pk_arrays(cs, td):
         hs.append(t)
         t = t * td.tau % B.R_MOD
     singles = fb1([td.alpha, td.beta, td.delta])
-    singles2 = fb2([td.beta, td.delta])
+    singles2 = fb2([td.beta, td.delta, td.gamma])
+    ginv = B.fr_inv(td.gamma)
     return {"alpha_g1": singles[0], "beta_g1": singles[1], "delta_g1": singles[2], "beta_g2": singles2[0], "delta_g2": singles2[1],
+            "gamma_g2": singles2[2], "gamma_abc_g1": fb1([abc[i] * ginv for i in range(ni)]),
             "a_query": fb1(a), "b_g1_query": fb1(b), "b_g2_query": fb2(b), "h_query": fb1(hs),
             "l_query": fb1([abc[i] * dinv for i in range(ni, m)]) if m > ni else np.zeros((0, 24), dtype=np.uint32)}
 
@@ -58,3 +60,34 @@ def dlog_expected_proof(dl, r1cs, z, h, r, s):
 def proof_to_py(proof):
     a, b, c = proof
     return ark.g1_to_py(a)[0], ark.g2_to_py(b)[0], ark.g1_to_py(c)[0]
+
+
+def trapdoor_words(td):
+    """oracle.py Trapdoor -> the word arrays ctg.Context.generate_parameters takes (ctg_trapdoor)."""
+    d = {k: ark.fr_mont_from_ints([getattr(td, k)])[0] for k in ("alpha", "beta", "gamma", "delta", "tau")}
+    d["g1"] = ark.g1_from_py([td.g1])[0]
+    d["g2"] = ark.g2_from_py([td.g2])[0]
+    return d
+
+
+def groth16_verify_words(key, proof, public_inputs):
+    """Pairing check (oracle/py/pairing.py) of a proof given as word arrays against a key dict of word arrays
+    holding alpha_g1, beta_g2, gamma_g2, delta_g2, gamma_abc_g1.  public_inputs: ints, without the constant 1."""
+    from oracle.py import pairing as PR
+    a, b, c = proof_to_py(proof)
+    return PR.groth16_verify(ark.g1_to_py(key["alpha_g1"])[0], ark.g2_to_py(key["beta_g2"])[0], ark.g2_to_py(key["gamma_g2"])[0],
+                             ark.g2_to_py(key["delta_g2"])[0], ark.g1_to_py(key["gamma_abc_g1"]), (a, b, c), public_inputs)
+
+
+def cs_from_arrays(r1cs):
+    """Array-dict R1CS (ctg.synthetic / ark.r1cs_from_py layout) -> oracle.py.groth16.R1CS with integer coefficients."""
+    cs = G.R1CS(num_instance=r1cs["num_instance"], num_witness=r1cs["num_witness"])
+    for name in "abc":
+        m = r1cs[name]
+        vals = ark.fr_ints_from_mont(m["val"]) if len(m["col"]) else []
+        rows = []
+        for i in range(r1cs["num_constraints"]):
+            lo, hi = int(m["row_ptr"][i]), int(m["row_ptr"][i + 1])
+            rows.append([(vals[k], int(m["col"][k])) for k in range(lo, hi)])
+        setattr(cs, name, rows)
+    return cs
