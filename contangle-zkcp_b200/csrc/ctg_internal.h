@@ -104,6 +104,16 @@ struct ctg_ctx {
 
 struct ctg_bases { ctg::Bases b; };
 
+// ark_groth16::ProvingKey (+ VerifyingKey) resident in HBM in arkworks' order: produced by key generation (setup.cu) or by
+// reading a circuit.zkey image (codec.cu)
+struct ctg_params {
+  uint64_t ni = 0, nw = 0, nc = 0, m = 0, n = 0;
+  ctg::G1Affine *a_query = nullptr, *b_g1_query = nullptr, *h_query = nullptr, *l_query = nullptr, *gamma_abc_g1 = nullptr;
+  ctg::G2Affine* b_g2_query = nullptr;
+  ctg::G1Affine* singles_g1 = nullptr;  // alpha_g1, beta_g1, delta_g1
+  ctg::G2Affine* singles_g2 = nullptr;  // beta_g2, gamma_g2, delta_g2
+};
+
 namespace ctg {
 
 #define CTG_CUDA(ctx, call)                                                                  \
@@ -144,6 +154,10 @@ int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t 
 int32_t fr_pow_table(ctg_ctx* ctx, Fr* d_out, uint64_t n, const Fr& base, const Fr& scale, cudaStream_t st);  // out[i] = scale * base^i
 Fr fr_root_of_unity(int log_n);   // generator of the 2^log_n domain (ark-poly Radix2EvaluationDomain::group_gen), Montgomery
 Fr fr_from_u64(uint64_t x);
+
+// setup.cu
+void params_free(ctg_params* p);
+int32_t params_alloc(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, uint64_t n, ctg_params** out);   // device arrays sized, contents undefined
 
 // msm_g1.cu / msm_g2.cu
 MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes);

@@ -14,15 +14,6 @@
 
 #include "ctg_internal.h"
 
-struct ctg_params {
-  uint64_t ni = 0, nw = 0, nc = 0, m = 0, n = 0;
-  // device arrays in arkworks' order
-  ctg::G1Affine *a_query = nullptr, *b_g1_query = nullptr, *h_query = nullptr, *l_query = nullptr, *gamma_abc_g1 = nullptr;
-  ctg::G2Affine* b_g2_query = nullptr;
-  ctg::G1Affine* singles_g1 = nullptr;  // alpha_g1, beta_g1, delta_g1
-  ctg::G2Affine* singles_g2 = nullptr;  // beta_g2, gamma_g2, delta_g2
-};
-
 namespace ctg {
 
 static constexpr int kWarp = 32;
@@ -186,6 +177,22 @@ void params_free(ctg_params* p) {
   delete p;
 }
 
+int32_t params_alloc(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, uint64_t n, ctg_params** out) {
+  ctg_params* p = new ctg_params();
+  const uint64_t m = ni + nw;
+  p->ni = ni; p->nw = nw; p->nc = nc; p->m = m; p->n = n;
+  auto alloc = [&](void** dst, size_t bytes) { if (cudaMalloc(dst, bytes ? bytes : 16) != cudaSuccess) { cudaGetLastError(); return false; } return true; };
+  if (!alloc((void**)&p->a_query, m * sizeof(G1Affine)) || !alloc((void**)&p->b_g1_query, m * sizeof(G1Affine)) ||
+      !alloc((void**)&p->b_g2_query, m * sizeof(G2Affine)) || !alloc((void**)&p->h_query, (n - 1) * sizeof(G1Affine)) ||
+      !alloc((void**)&p->l_query, nw * sizeof(G1Affine)) || !alloc((void**)&p->gamma_abc_g1, ni * sizeof(G1Affine)) ||
+      !alloc((void**)&p->singles_g1, 3 * sizeof(G1Affine)) || !alloc((void**)&p->singles_g2, 3 * sizeof(G2Affine))) {
+    params_free(p);
+    return fail(ctx, CTG_ERR_OOM, "params: cudaMalloc failed");
+  }
+  *out = p;
+  return CTG_OK;
+}
+
 int32_t generate_parameters(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, const ctg_csr* const mats[3], const ctg_trapdoor* td, ctg_params** out) {
   if (!td || !out) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: null argument");
   if (ni == 0) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: num_instance includes the constant 1 and must be >= 1");
@@ -210,15 +217,9 @@ int32_t generate_parameters(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc,
   NttDomain* dom;
   CTG_TRY(ntt_get_domain(ctx, log_n, &dom));
 
-  ctg_params* p = new ctg_params();
-  p->ni = ni; p->nw = nw; p->nc = nc; p->m = m; p->n = n;
+  ctg_params* p = nullptr;
+  CTG_TRY(params_alloc(ctx, ni, nw, nc, n, &p));
   struct Guard { ctg_params* p; ~Guard() { if (p) params_free(p); } } guard{p};
-  auto alloc = [&](void** dst, size_t bytes) { if (cudaMalloc(dst, bytes ? bytes : 16) != cudaSuccess) { cudaGetLastError(); return false; } return true; };
-  if (!alloc((void**)&p->a_query, m * sizeof(G1Affine)) || !alloc((void**)&p->b_g1_query, m * sizeof(G1Affine)) ||
-      !alloc((void**)&p->b_g2_query, m * sizeof(G2Affine)) || !alloc((void**)&p->h_query, (n - 1) * sizeof(G1Affine)) ||
-      !alloc((void**)&p->l_query, nw * sizeof(G1Affine)) || !alloc((void**)&p->gamma_abc_g1, ni * sizeof(G1Affine)) ||
-      !alloc((void**)&p->singles_g1, 3 * sizeof(G1Affine)) || !alloc((void**)&p->singles_g2, 3 * sizeof(G2Affine)))
-    return fail(ctx, CTG_ERR_OOM, "generate_parameters: cudaMalloc failed");
 
   // scalars
   DevBuf d_L, d_u, d_v, d_w, d_abc, d_hs, d_single;

@@ -35,6 +35,8 @@ EXPORTS = [
     "ctg_r1cs_free", "ctg_witness_map", "ctg_prove", "ctg_prove_batch", "ctg_pk_upload_shard", "ctg_prove_partial",
     "ctg_prove_combine", "ctg_prepare_inputs", "ctg_host_alloc", "ctg_host_free",
     "ctg_generate_parameters", "ctg_params_pk_view", "ctg_params_download", "ctg_params_free",
+    "ctg_params_deserialize_unchecked", "ctg_params_serialize_unchecked", "ctg_params_serialize_vk",
+    "ctg_proof_serialize", "ctg_proof_deserialize",
 ]
 
 
@@ -349,6 +351,16 @@ class Context:
             n *= 2
         return DeviceParams(self, h, r1cs["num_instance"], r1cs["num_witness"], r1cs["num_constraints"], n)
 
+    def load_proving_key(self, key_image: bytes):
+        """ProvingKey::deserialize_unchecked of a circuit.zkey image (lib/src/utils.rs:104-110), decoded on the device."""
+        buf = np.frombuffer(key_image, dtype=np.uint8)
+        h = C.c_void_p()
+        self._check(load().ctg_params_deserialize_unchecked(self.h, C.c_void_p(buf.ctypes.data), C.c_uint64(buf.size), C.byref(h)))
+        v, gl = PkView(), C.c_uint64()
+        self._check(load().ctg_params_pk_view(self.h, h, C.byref(v), None, C.byref(gl)))
+        ni, m, n = int(gl.value), int(v.a_len), int(v.h_len) + 1
+        return DeviceParams(self, h, ni, m - ni, n - ni, n)
+
     def upload_r1cs(self, r1cs: dict):
         mats, keep = self._csr_triplet(r1cs)
         h = C.c_void_p()
@@ -479,7 +491,43 @@ class DeviceParams:
         self.ctx._check(load().ctg_params_download(self.ctx.h, self.handle, C.byref(dst)))
         return out
 
+    def _serialize(self, fn):
+        n = C.c_uint64()
+        self.ctx._check(fn(self.ctx.h, self.handle, None, C.c_uint64(0), C.byref(n)))
+        out = np.zeros(int(n.value), dtype=np.uint8)
+        self.ctx._check(fn(self.ctx.h, self.handle, C.c_void_p(out.ctypes.data), C.c_uint64(out.size), C.byref(n)))
+        return out.tobytes()
+
+    def serialize_unchecked(self):
+        """circuit.zkey image: ProvingKey::serialize_unchecked (lib/src/utils.rs:91)."""
+        return self._serialize(load().ctg_params_serialize_unchecked)
+
+    def serialize_vk(self):
+        """verification.key image: VerifyingKey::serialize, compressed (lib/src/utils.rs:94)."""
+        return self._serialize(load().ctg_params_serialize_vk)
+
     def free(self):
         if self.handle:
             load().ctg_params_free(self.ctx.h, self.handle)
             self.handle = None
+
+
+def proof_to_bytes(proof):
+    """ark_to_bytes(proof): 192 compressed bytes.  proof = (a, b, c) word arrays.  Host-only."""
+    a, b, c = proof
+    buf = np.concatenate([_arr(a).reshape(G1_W), _arr(b).reshape(G2_W), _arr(c).reshape(G1_W)])
+    out = np.zeros(192, dtype=np.uint8)
+    if load().ctg_proof_serialize(_ptr(buf), C.c_void_p(out.ctypes.data)) != 0:
+        raise CtgError("proof_serialize failed")
+    return out.tobytes()
+
+
+def proof_from_bytes(data, check_subgroup=True):
+    """ark_from_bytes::<Proof>: decompress (square roots) and, as arkworks' checked deserialize, test the subgroup."""
+    raw = np.frombuffer(bytes(data), dtype=np.uint8)
+    if raw.size != 192:
+        raise CtgError("proof_from_bytes: expected 192 bytes")
+    out = np.zeros(G1_W + G2_W + G1_W, dtype=np.uint32)
+    if load().ctg_proof_deserialize(C.c_void_p(raw.ctypes.data), int(bool(check_subgroup)), _ptr(out)) != 0:
+        raise CtgError("proof_from_bytes: invalid encoding (arkworks: SerializationError::InvalidData)")
+    return out[:G1_W].copy(), out[G1_W:G1_W + G2_W].copy(), out[G1_W + G2_W:].copy()

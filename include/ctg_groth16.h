@@ -249,6 +249,22 @@ int32_t ctg_params_pk_view(ctg_ctx* ctx, const ctg_params* params, ctg_pk_view* 
 int32_t ctg_params_download(ctg_ctx* ctx, const ctg_params* params, const ctg_params_out* dst);
 void ctg_params_free(ctg_ctx* ctx, ctg_params* params);
 
+/* ---- arkworks canonical wire formats (ark-serialize 0.3 conventions, see csrc/codec.cu) --------------
+ * circuit.zkey = ProvingKey::serialize_unchecked (lib/src/utils.rs:85-110): decoded ON THE DEVICE straight into the packed
+ * Montgomery layout (a ctg_params, then ctg_params_pk_view -> ctg_pk_upload), or encoded from it.  Passing out = NULL to a
+ * serialize call only reports the size in *written.  verification.key = VerifyingKey::serialize (compressed,
+ * lib/src/utils.rs:94).  Reading rejects non-canonical field elements and invalid flag bits with CTG_ERR_INVALID
+ * (arkworks: SerializationError::InvalidData); like deserialize_unchecked it does not test curve or subgroup membership. */
+int32_t ctg_params_deserialize_unchecked(ctg_ctx* ctx, const uint8_t* key_image, uint64_t len, ctg_params** out);
+int32_t ctg_params_serialize_unchecked(ctg_ctx* ctx, const ctg_params* params, uint8_t* out, uint64_t capacity, uint64_t* written);
+int32_t ctg_params_serialize_vk(ctg_ctx* ctx, const ctg_params* params, uint8_t* out, uint64_t capacity, uint64_t* written);
+/* Proof::serialize / Proof::deserialize (compressed, 48 + 96 + 48 = 192 bytes: ark_to_bytes / ark_from_bytes,
+ * circuits-ark/src/utils.rs:12-22; lib/src/zk/encryption.rs:78-84,135-141).  Host-only, no context needed.
+ * check_subgroup != 0 adds arkworks' r * P == O test of the checked deserialize. */
+#define CTG_PROOF_BYTES 192
+int32_t ctg_proof_serialize(const ctg_proof* proof, uint8_t* out192);
+int32_t ctg_proof_deserialize(const uint8_t* in192, int check_subgroup, ctg_proof* out);
+
 #ifdef __cplusplus
 }
 #endif
