@@ -329,7 +329,7 @@ def extras(ctx, torch, dev, stream, S, args):
     out["ntt_note"] = ("radix-2 NTT over a 255-bit field is integer-bound on B200: 68*log2(n) MAC32 per element against 64 B of "
                        "compulsory traffic; frac_of_mac32_peak is the binding roofline, frac_of_hbm_peak the one the north star names")
     msm = {}
-    for lg in (16, 18, 20):
+    for lg in (16, 18, 20, 24):
         n = 1 << lg
         b = ctx.bases_progression_g1(S.g1_gen_words(), S.fr_mont([77 + lg])[0], S.fr_mont([3])[0], n, copies=args.copies)
         sc = torch.randint(0, 1 << 30, (n, 8), device=dev, dtype=torch.int32)
@@ -351,35 +351,61 @@ def extras(ctx, torch, dev, stream, S, args):
         out[f"g2_msm_device_resident_2^{lg}"] = {"ms": ms, "Mpts_per_s": n / (ms * 1e-3) / 1e6, "sort_ms": t["msm_sort_ms"], "accumulate_ms": acc_ms,
                                                   "reduce_ms": t["msm_reduce_ms"], "accumulate_frac_of_mac32_peak": n * 134400.0 / (acc_ms * 1e-3) / mac_peak}
         b.free()
-    # Groth16 prove (configs 3/4 shape, MulChain) with device-resident key and R1CS
-    for lg in (16, 20, 22):
+    # Groth16 setup + prove (configs 3/4 shape, MulChain): the key is GENERATED on the device (ctg_generate_parameters, a real
+    # Groth16 key for the circuit) and handed to the prover's key cache device-to-device; assignment in pinned host memory
+    from oracle import ark as _ark  # checker / cpu_baseline leg only
+    td_words, _ = S.trapdoor()
+    for lg in (16, 18, 20, 22):
         r1cs, zm, _ = S.mul_chain(lg)
-        pk, _ = S.progression_pk(ctx, r1cs)
-        dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], copies=args.copies)
+        t0 = time.perf_counter()
+        dp = ctx.generate_parameters(r1cs, td_words)
+        setup_ms = (time.perf_counter() - t0) * 1e3
+        row = {"setup_wall_ms": setup_ms}
+        if lg == 20:   # circuit.zkey image: encode on the device, then decode (what a prover process does at start-up)
+            image = dp.serialize_unchecked()
+            t0 = time.perf_counter()
+            dp2 = ctx.load_proving_key(image)
+            dt = time.perf_counter() - t0
+            row["zkey_bytes"] = len(image)
+            row["zkey_load_wall_ms"] = dt * 1e3
+            row["zkey_load_GBps"] = len(image) / dt / 1e9
+            dp2.free()
+            del image
+        key_host = dp.download() if lg <= 18 else None
+        dpk = dp.to_device_pk(copies=args.copies)
+        dp.free()
         dr = ctx.upload_r1cs(r1cs)
-        del pk
-        zm = ctx.pinned_like(zm)      # the assignment sits in page-locked memory (ctg_host_alloc), as the Rust shim packs it
+        zp = ctx.pinned_like(zm)      # the assignment sits in page-locked memory (ctg_host_alloc), as the Rust shim packs it
         r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
         for _ in range(2):
-            ctx.prove(dpk, dr, zm, r, s)
+            proof = ctx.prove(dpk, dr, zp, r, s)
         ts = []
         for _ in range(5):
             t0 = time.perf_counter()
-            _, tm = ctx.prove(dpk, dr, zm, r, s, timed=True)
+            _, tm = ctx.prove(dpk, dr, zp, r, s, timed=True)
             ts.append(((time.perf_counter() - t0) * 1e3, tm))
         ts.sort(key=lambda x: x[0])
         wall, tm = ts[len(ts) // 2]
-        out[f"groth16_prove_mulchain_2^{lg}"] = {"wall_ms_median": wall, "stages_ms": {k: v for k, v in tm.items() if not k.startswith("msm_sort") and not k.startswith("msm_acc") and not k.startswith("msm_red")},
-                                                 "note": "the five MSMs run on five streams: stage times overlap and do not add up to total_ms"}
-        ctx.pinned_free(zm)
+        row.update({"wall_ms_median": wall, "stages_ms": {k: v for k, v in tm.items() if not k.startswith("msm_sort") and not k.startswith("msm_acc") and not k.startswith("msm_red")},
+                    "note": "the five MSMs run on five streams: stage times overlap and do not add up to total_ms"})
+        if key_host is not None:   # the same proof on the host cores: arkworks-0.3.0 algorithm restated in C++ (oracle/c), all threads
+            t0 = time.perf_counter()
+            want = _ark.create_proof(key_host, r1cs, zm, r, s)
+            cpu_ms = (time.perf_counter() - t0) * 1e3
+            row["cpu_port_prove_ms"] = cpu_ms
+            row["cpu_cores"] = _ark.threads()
+            row["gpu_over_cpu"] = cpu_ms / wall
+            row["gpu_matches_cpu"] = bool(all(np.array_equal(g, w) for g, w in zip(proof, want)))
+        out[f"groth16_prove_mulchain_2^{lg}"] = row
+        ctx.pinned_free(zp)
         dpk.free(); dr.free()
     # config 5 shape at one GPU: batched PoE-shaped proofs with a device-resident key (proofs/s)
     for n_data in (1, 100):
         r1cs, zm, _ = S.poe_shape(n_data)
-        pk, _ = S.progression_pk(ctx, r1cs)
-        dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], copies=args.copies)
+        dp = ctx.generate_parameters(r1cs, td_words)
+        dpk = dp.to_device_pk(copies=args.copies)
+        dp.free()
         dr = ctx.upload_r1cs(r1cs)
-        del pk
         nb = 32
         zb = np.ascontiguousarray(np.broadcast_to(zm, (nb,) + zm.shape))
         rs = np.ascontiguousarray(np.broadcast_to(np.stack([S.fr_mont([3])[0], S.fr_mont([5])[0]]), (nb, 2, 8)))

@@ -198,3 +198,14 @@ def progression_pk(ctx, r1cs, seed=0xC0FFEE):
     pk["a_query"] = query(1, "a", m); pk["b_g1_query"] = query(1, "b", m); pk["b_g2_query"] = query(2, "b", m)
     pk["h_query"] = query(1, "h", n - 1); pk["l_query"] = query(1, "l", nw)
     return pk, dl
+
+
+def trapdoor(seed=0xC0FFEE):
+    """A seeded Groth16 trapdoor for Context.generate_parameters: Montgomery words alpha, beta, gamma, delta, tau and the
+    standard generators (arkworks draws random generators; any subgroup generator gives a valid key).  Returns
+    (words dict, ints dict)."""
+    rng = SplitMix64(seed ^ 0x7D00)
+    ints = {k: rng.fr() or 1 for k in ("alpha", "beta", "gamma", "delta", "tau")}
+    words = {k: fr_mont([v])[0] for k, v in ints.items()}
+    words["g1"], words["g2"] = g1_gen_words(), g2_gen_words()
+    return words, ints
