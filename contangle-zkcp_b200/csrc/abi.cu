@@ -16,6 +16,8 @@ int32_t imad_probe(ctg_ctx* ctx, double* imad_per_s, double* fq_mul_per_s);
 int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, int shard_index, int shard_count, ctg_pk** out);
 int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch, ctg_proof* out);
 int32_t prove_partial(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, void* out_partials, ctg_timings* tm);
+int32_t prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, uint32_t chain_mask, void* d_abc);
+int32_t prove_partial_finish(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* rr, const ctg_fr* ss, void* d_abc, void* out_partials);
 int32_t prove_combine(ctg_ctx* ctx, const void* host_partials, uint32_t k, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out);
 void lanes_destroy(ctg_ctx* ctx);
 void pk_free(ctg_pk* pk);
@@ -500,6 +502,16 @@ int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* 
   int32_t rc = prove_partial(ctx, pk_shard, r1cs, z, r, s, out, timings ? &local : nullptr);
   if (rc == CTG_OK && timings) { *timings = local; g_last_timings = local; }
   return rc;
+}
+int32_t ctg_prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
+                                uint32_t chain_mask, void* d_abc) {
+  if (!ctx) return CTG_ERR_INVALID;
+  return prove_partial_begin(ctx, pk_shard, r1cs, z, r, s, chain_mask, d_abc);
+}
+int32_t ctg_prove_partial_finish(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* r, const ctg_fr* s, void* d_abc,
+                                 ctg_proof_partial* out) {
+  if (!ctx) return CTG_ERR_INVALID;
+  return prove_partial_finish(ctx, pk_shard, r1cs, r, s, d_abc, out);
 }
 int32_t ctg_prove_combine(ctg_ctx* ctx, const ctg_proof_partial* partials, uint32_t k, const ctg_fr* r, const ctg_fr* s, ctg_proof* out) {
   if (!ctx) return CTG_ERR_INVALID;

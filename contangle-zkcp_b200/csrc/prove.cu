@@ -276,20 +276,27 @@ void r1cs_free(ctg_r1cs* r) {
 // ---- host: witness map ------------------------------------------------------------------------
 // d_z: m (+3) Montgomery elements on the device.  d_abc: 3 * n scratch.  Leaves h (bit-reversed,
 // Montgomery) in d_abc[0..n).
-static int32_t witness_map_dev(ctg_ctx* ctx, const ctg_r1cs* r, const Fr* d_z, Fr* d_abc, cudaStream_t st) {
+// chain k (0 = a, 1 = b, 2 = c): SpMV, then ifft + coset_fft fused -> coset evaluations in v (n elements, natural order)
+static int32_t witness_chain_dev(ctg_ctx* ctx, const ctg_r1cs* r, const Fr* d_z, Fr* v, int k, cudaStream_t st) {
+  const uint64_t n = r->n;
+  spmv_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(r->row_ptr[k], r->col[k], r->val[k], d_z, v, r->nc, r->ni, n, k == 0);
+  CTG_KERNEL_CHECK(ctx);
+  return ntt_ifft_then_coset_fft(ctx, v, r->log_n, st);
+}
+// (a b - c) / Z on the coset, then coset_ifft: h (bit-reversed, Montgomery) in d_abc[0..n)
+static int32_t witness_finish_dev(ctg_ctx* ctx, const ctg_r1cs* r, Fr* d_abc, cudaStream_t st) {
   const uint64_t n = r->n;
   NttDomain* dom;
   CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
-  Fr* v[3] = {d_abc, d_abc + n, d_abc + 2 * n};
-  const unsigned blocks = (unsigned)((n + 127) / 128);
-  for (int k = 0; k < 3; k++) {
-    spmv_kernel<<<blocks, 128, 0, st>>>(r->row_ptr[k], r->col[k], r->val[k], d_z, v[k], r->nc, r->ni, n, k == 0);
-    CTG_KERNEL_CHECK(ctx);
-    CTG_TRY(ntt_ifft_then_coset_fft(ctx, v[k], r->log_n, st));
-  }
-  pointwise_kernel<<<blocks, 128, 0, st>>>(v[0], v[1], v[2], dom->zinv, n);
+  pointwise_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_abc, d_abc + n, d_abc + 2 * n, dom->zinv, n);
   CTG_KERNEL_CHECK(ctx);
-  return ntt_coset_ifft_bitrev(ctx, v[0], r->log_n, st);
+  return ntt_coset_ifft_bitrev(ctx, d_abc, r->log_n, st);
+}
+static int32_t witness_map_dev(ctg_ctx* ctx, const ctg_r1cs* r, const Fr* d_z, Fr* d_abc, cudaStream_t st) {
+  NttDomain* dom;
+  CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));  // tables are built (and synchronised) before any chain is enqueued
+  for (int k = 0; k < 3; k++) CTG_TRY(witness_chain_dev(ctx, r, d_z, d_abc + (uint64_t)k * r->n, k, st));
+  return witness_finish_dev(ctx, r, d_abc, st);
 }
 
 int32_t witness_map_host(ctg_ctx* ctx, const ctg_r1cs* r, const ctg_fr* z, ctg_fr* h_out) {
@@ -357,7 +364,9 @@ static int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
 //   d_proof_out != nullptr : full proof (shard_count must be 1), written to device memory d_proof_out
 //   d_partials_out != nullptr : this shard's partial sums [A, B1, L, H] (4 G1 XYZZ) then B2 (G2 XYZZ), 1152 bytes
 static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const Fr& r_m, const Fr& s_m,
-                             ctg_proof* host_proof_out, void* host_partials_out, bool timed) {
+                             ctg_proof* host_proof_out, void* host_partials_out, bool timed,
+                             int phase = 0 /* 0 = whole proof, 1 = up to the coset evaluations, 2 = the rest */, uint32_t chain_mask = 7,
+                             Fr* d_abc_ext = nullptr /* caller-owned 3n buffer for the a, b, c chains (multi-GPU exchange) */) {
   CTG_TRY(lane_init(ctx, lane_idx));
   ProveLane& L = ctx->lanes[lane_idx];
   const uint64_t n = r->n, m = pk->m;
@@ -368,6 +377,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   Fr* d_z = (Fr*)L.scratch;
   Fr* d_abc = d_z + (m + 3);
   char* tail = (char*)(d_abc + 3 * n);
+  if (d_abc_ext) d_abc = d_abc_ext;
   tail = (char*)(((uintptr_t)tail + 63) & ~(uintptr_t)63);
   G1XYZZ* d_g1 = (G1XYZZ*)tail;           // [0]=A [1]=B1 [2]=L [3]=H
   G2XYZZ* d_g2 = (G2XYZZ*)(d_g1 + 4);
@@ -375,6 +385,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   cudaStream_t s0 = L.st[0];
   int ne = 0;
   auto mark = [&](cudaStream_t st) { if (timed && ne < 16) cudaEventRecord(L.ev_t[ne], st); ne++; };
+  if (phase != 2) {
   mark(s0);                                                                   // 0
   CTG_CUDA(ctx, cudaMemcpyAsync(d_z, z, m * sizeof(Fr), cudaMemcpyHostToDevice, s0));
   set_tail_kernel<<<1, 32, 0, s0>>>(d_z, m, r_m, s_m);
@@ -396,8 +407,17 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
     mark(st);                                                                 // 3,5,7,9
     CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
   }
-  // witness map and the H MSM on the lane's main stream
-  CTG_TRY(witness_map_dev(ctx, r, d_z, d_abc, s0));
+  // witness map on the lane's main stream: the coset evaluations of a, b, c (the chains this rank owns) ...
+  NttDomain* dom;
+  CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
+  for (int k = 0; k < 3; k++)
+    if (chain_mask & (1u << k)) CTG_TRY(witness_chain_dev(ctx, r, d_z, d_abc + (uint64_t)k * n, k, s0));
+  if (phase == 1) return CTG_OK;
+  } else {
+    ne = 10;
+  }
+  // ... then (a b - c)/Z, the coset_ifft and the H MSM
+  CTG_TRY(witness_finish_dev(ctx, r, d_abc, s0));
   set_h_tail_kernel<<<1, 32, 0, s0>>>(d_abc, n, r_m, s_m);
   CTG_KERNEL_CHECK(ctx);
   mark(s0);                                                                   // 10
@@ -484,6 +504,31 @@ int32_t prove_partial(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const c
   CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, nullptr, out_partials, tm != nullptr));
   CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));
   if (tm) lane_timings(ctx->lanes[0], tm);
+  return CTG_OK;
+}
+
+// Multi-GPU witness map: phase 1 computes only the chains in chain_mask into the caller's buffer; the caller exchanges the
+// chains between ranks (NCCL broadcast over NVLink); phase 2 finishes.  Both phases use lane 0.
+int32_t prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, uint32_t chain_mask, void* d_abc) {
+  if (!pk || !r || !z || !rr || !ss || !d_abc) return fail(ctx, CTG_ERR_INVALID, "prove_partial_begin: null argument");
+  if (chain_mask > 7) return fail(ctx, CTG_ERR_INVALID, "prove_partial_begin: chain_mask has bits beyond a, b, c");
+  CTG_TRY(check_prove_args(ctx, pk, r));
+  Fr r_m, s_m;
+  memcpy(&r_m, rr, sizeof(Fr));
+  memcpy(&s_m, ss, sizeof(Fr));
+  CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, nullptr, nullptr, false, 1, chain_mask, (Fr*)d_abc));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));   // the chains are complete: safe to hand to a collective on any stream
+  return CTG_OK;
+}
+int32_t prove_partial_finish(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* rr, const ctg_fr* ss, void* d_abc, void* out_partials) {
+  if (!pk || !r || !rr || !ss || !d_abc || !out_partials) return fail(ctx, CTG_ERR_INVALID, "prove_partial_finish: null argument");
+  CTG_TRY(check_prove_args(ctx, pk, r));
+  if (!ctx->lanes[0].ready) return fail(ctx, CTG_ERR_STATE, "prove_partial_finish without prove_partial_begin");
+  Fr r_m, s_m;
+  memcpy(&r_m, rr, sizeof(Fr));
+  memcpy(&s_m, ss, sizeof(Fr));
+  CTG_TRY(prove_enqueue(ctx, 0, pk, r, nullptr, r_m, s_m, nullptr, out_partials, false, 2, 0, (Fr*)d_abc));
+  CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));
   return CTG_OK;
 }
 

@@ -36,7 +36,7 @@ EXPORTS = [
     "ctg_prove_combine", "ctg_prepare_inputs", "ctg_host_alloc", "ctg_host_free",
     "ctg_generate_parameters", "ctg_params_pk_view", "ctg_params_download", "ctg_params_free",
     "ctg_params_deserialize_unchecked", "ctg_params_serialize_unchecked", "ctg_params_serialize_vk",
-    "ctg_proof_serialize", "ctg_proof_deserialize",
+    "ctg_proof_serialize", "ctg_proof_deserialize", "ctg_prove_partial_begin", "ctg_prove_partial_finish",
 ]
 
 
@@ -412,6 +412,23 @@ class Context:
         t = Timings()
         self._check(load().ctg_prove_partial(self.h, pk_shard.handle, r1cs.handle, _ptr(z), _ptr(r), _ptr(s), _ptr(out), C.byref(t) if timed else None))
         return (out, t.as_dict()) if timed else out
+
+    def prove_partial_begin(self, pk_shard: "DevicePk", r1cs: "DeviceR1cs", z, r, s, chain_mask, d_abc_ptr):
+        """Phase 1 of a sharded proof with a distributed witness map: computes the chains in chain_mask (bit 0 = a, 1 = b,
+        2 = c) into the caller's device buffer (3 * n Fr at d_abc_ptr) and starts the assignment MSMs."""
+        z = _arr(z, FR_W)
+        if z.shape[0] != r1cs.m or pk_shard.m != r1cs.m:
+            raise CtgError("prove_partial_begin: assignment / key / R1CS sizes differ")
+        r, s = _arr(r).reshape(FR_W), _arr(s).reshape(FR_W)
+        self._check(load().ctg_prove_partial_begin(self.h, pk_shard.handle, r1cs.handle, _ptr(z), _ptr(r), _ptr(s), C.c_uint32(chain_mask),
+                                                   C.c_void_p(d_abc_ptr)))
+
+    def prove_partial_finish(self, pk_shard: "DevicePk", r1cs: "DeviceR1cs", r, s, d_abc_ptr):
+        """Phase 2: pointwise step, coset_ifft and the H MSM; returns the (288,) words of partial sums."""
+        r, s = _arr(r).reshape(FR_W), _arr(s).reshape(FR_W)
+        out = np.zeros(PARTIAL_W, dtype=np.uint32)
+        self._check(load().ctg_prove_partial_finish(self.h, pk_shard.handle, r1cs.handle, _ptr(r), _ptr(s), C.c_void_p(d_abc_ptr), _ptr(out)))
+        return out
 
     def prove_combine(self, partials, r, s):
         """Sum the shards' partials (k, 288) and assemble the proof (A, B, C)."""

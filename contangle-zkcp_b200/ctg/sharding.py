@@ -42,10 +42,43 @@ def all_gather_partials(partial: np.ndarray, dist, device=None):
     return out.cpu().numpy().view(np.uint32).reshape(world, PARTIAL_W)
 
 
-def sharded_prove(ctx, pk_shard, r1cs, z, r, s, dist, device=None):
+def chain_owners(world: int):
+    """Rank that computes each of the three witness-map chains (a, b, c): spread over the first three ranks."""
+    if world < 1:
+        raise ValueError("bad world size")
+    return [k % world for k in range(3)]
+
+
+def chain_mask(rank: int, world: int) -> int:
+    """Bit k set when `rank` owns chain k (ctg_prove_partial_begin's chain_mask)."""
+    return sum(1 << k for k, o in enumerate(chain_owners(world)) if o == rank)
+
+
+def exchange_chains(abc, dist):
+    """Broadcast chain k of `abc` (a (3, n, 8) int32 tensor: the coset evaluations of a, b, c) from its owner rank, so that
+    every rank ends up with all three.  NCCL over NVLink for CUDA tensors, gloo for CPU tensors."""
+    for k, owner in enumerate(chain_owners(dist.get_world_size())):
+        dist.broadcast(abc[k], src=owner)
+    return abc
+
+
+def sharded_prove(ctx, pk_shard, r1cs, z, r, s, dist, device=None, distribute_ntt=None):
     """ark_groth16::create_proof over `world` GPUs.  Every rank calls this with its own context and key shard and the
-    same (z, r, s); rank 0 returns (A, B, C), the other ranks return None."""
-    part = ctx.prove_partial(pk_shard, r1cs, z, r, s)
+    same (z, r, s); rank 0 returns (A, B, C), the other ranks return None.
+    distribute_ntt (default: on for NCCL with more than one rank): the three NTT chains of the witness map are computed by
+    their owner ranks and broadcast over NVLink (n * 32 bytes each) instead of being replicated on every rank."""
+    world = dist.get_world_size()
+    if distribute_ntt is None:
+        distribute_ntt = device is not None and world > 1
+    if distribute_ntt:
+        import torch
+        abc = torch.empty((3, r1cs.n, 8), dtype=torch.int32, device=device)
+        ctx.prove_partial_begin(pk_shard, r1cs, z, r, s, chain_mask(dist.get_rank(), world), abc.data_ptr())
+        exchange_chains(abc, dist)
+        torch.cuda.current_stream(device).synchronize()
+        part = ctx.prove_partial_finish(pk_shard, r1cs, r, s, abc.data_ptr())
+    else:
+        part = ctx.prove_partial(pk_shard, r1cs, z, r, s)
     allp = all_gather_partials(part, dist, device)
     if dist.get_rank() == 0:
         return ctx.prove_combine(allp, r, s)

@@ -220,6 +220,18 @@ int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, ui
 int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
                           ctg_proof_partial* out, ctg_timings* timings /* may be NULL */);
 int32_t ctg_prove_combine(ctg_ctx* ctx, const ctg_proof_partial* partials, uint32_t k, const ctg_fr* r, const ctg_fr* s, ctg_proof* out);
+/* The same with the witness map distributed over the ranks (the seven NTTs of R1CStoQAP::witness_map form three independent
+ * chains a, b, c -- SpMV, ifft, coset_fft -- joined by the pointwise step and the last coset_ifft).
+ *   begin : uploads z, starts this shard's A / B1 / B2 / L MSMs, and computes the chains in chain_mask (bit 0 = a, 1 = b, 2 = c)
+ *           into d_abc[k * n .. (k + 1) * n) -- a DEVICE buffer of 3 * n Fr owned by the caller; returns when they are complete;
+ *   (the caller broadcasts each chain from its owner to every rank: NCCL over NVLink, n * 32 bytes per chain; the MSMs
+ *    started by begin keep the SMs busy meanwhile)
+ *   finish: (a b - c)/Z, coset_ifft, this shard's H MSM; writes the 1152 bytes of partial sums.
+ * begin(chain_mask = 7) + finish with no exchange equals ctg_prove_partial.  One begin/finish pair in flight per context. */
+int32_t ctg_prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
+                                uint32_t chain_mask, void* d_abc);
+int32_t ctg_prove_partial_finish(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* r, const ctg_fr* s, void* d_abc,
+                                 ctg_proof_partial* out);
 
 /* ---- key generation ---------------------------------------------------------------
  * ark_groth16::generate_parameters(circuit, alpha, beta, gamma, delta, g1_generator, g2_generator, rng) after synthesis

@@ -548,3 +548,49 @@ def test_generate_parameters_rejects_bad_trapdoor(ctx):
     bad["a"] = dict(r1cs["a"]); bad["a"]["col"] = r1cs["a"]["col"].copy(); bad["a"]["col"][0] = 10**6
     with pytest.raises(ctg.CtgError):
         ctx.generate_parameters(bad, util.trapdoor_words(td))
+
+
+# ----------------------------------------------------------------------------- distributed witness map
+@pytest.mark.parametrize("log_n,shards", [(6, 1), (11, 3)])
+def test_prove_partial_begin_finish_with_chain_masks(ctx, log_n, shards):
+    """ctg_prove_partial_begin / _finish: (1) all chains on this rank; (2) chains computed in two separate begins (masks 0b001
+    and 0b110, what two ranks would do) and stitched together.  Partial sums are projective (their representation depends on
+    the order atomics filled the buckets in), so the comparison is on the combined, affine proof."""
+    import torch
+    r1cs, zm, _ = S.mul_chain(log_n)
+    pk, _ = S.progression_pk(ctx, r1cs)
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD))
+    full = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"])
+    want = ctx.prove(full, dr, zm, r, s)
+    full.free()
+    dev = torch.device("cuda", 0)
+    abc = torch.zeros((3, dr.n, 8), dtype=torch.int32, device=dev)
+    whole, stitched = [], []
+    for index in range(shards):
+        dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], shard=(index, shards))
+        abc.zero_(); torch.cuda.synchronize()
+        ctx.prove_partial_begin(dpk, dr, zm, r, s, 7, abc.data_ptr())
+        whole.append(ctx.prove_partial_finish(dpk, dr, r, s, abc.data_ptr()))
+        # rank "0": chain a only
+        abc.zero_(); torch.cuda.synchronize()
+        ctx.prove_partial_begin(dpk, dr, zm, r, s, 0b001, abc.data_ptr())
+        a_chain = abc[0].clone()
+        assert bool(a_chain.any()) and not bool(abc[1:].any())
+        torch.cuda.synchronize()
+        ctx.prove_partial_finish(dpk, dr, r, s, abc.data_ptr())   # drains the MSMs begin started; result unused
+        # rank "1": chains b and c, then the "broadcast" of a
+        abc.zero_(); torch.cuda.synchronize()
+        ctx.prove_partial_begin(dpk, dr, zm, r, s, 0b110, abc.data_ptr())
+        assert not bool(abc[0].any()) and bool(abc[1].any()) and bool(abc[2].any())
+        abc[0].copy_(a_chain)
+        torch.cuda.synchronize()
+        stitched.append(ctx.prove_partial_finish(dpk, dr, r, s, abc.data_ptr()))
+        with pytest.raises(ctg.CtgError):
+            ctx.prove_partial_begin(dpk, dr, zm, r, s, 8, abc.data_ptr())
+        dpk.free()
+    for parts in (whole, stitched):
+        got = ctx.prove_combine(np.stack(parts), r, s)
+        for g, w in zip(got, want):
+            assert np.array_equal(g, w)
+    dr.free()

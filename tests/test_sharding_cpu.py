@@ -92,6 +92,28 @@ def _worker(rank, world, port, q):
         allp = sharding.all_gather_partials(part, dist)
         assert allp.shape == (world, PARTIAL_W)
         assert np.array_equal(allp[rank], part)          # rank order preserved
+        # distributed witness map: each rank computes the chains it owns (oracle stand-in for ctg_prove_partial_begin),
+        # the exchange fills in the rest, and the finish step reproduces the oracle's h on every rank
+        import torch
+        mask = sharding.chain_mask(rank, world)
+        assert sum(sharding.chain_mask(k, world) for k in range(world)) == 7
+        abc = torch.zeros((3, n, 8), dtype=torch.int32)
+        zi = list(z)
+        for k, rows in enumerate((cs.a, cs.b, cs.c)):
+            if not mask & (1 << k):
+                continue
+            ev = [sum(cf * zi[j] for cf, j in row) % B.R_MOD for row in rows] + [0] * (n - len(rows))
+            if k == 0:
+                for j in range(ni):
+                    ev[cs.num_constraints + j] = zi[j]
+            v = ark.ntt_fr(ark.ntt_fr(ark.fr_mont_from_ints(ev), inverse=True), coset=True)
+            abc[k] = torch.from_numpy(v.view(np.int32).copy())
+        sharding.exchange_chains(abc, dist)
+        ev = [ark.fr_ints_from_mont(abc[k].numpy().view(np.uint32)) for k in range(3)]
+        zinv = pow((pow(7, n, B.R_MOD) - 1) % B.R_MOD, -1, B.R_MOD)
+        hq = [(x * y - w) % B.R_MOD * zinv % B.R_MOD for x, y, w in zip(*ev)]
+        h2 = ark.fr_ints_from_mont(ark.ntt_fr(ark.fr_mont_from_ints(hq), inverse=True, coset=True))
+        assert h2 == h, "distributed witness map differs from the oracle's"
         if rank == 0:
             def total(off, words, add):
                 acc = np.zeros(words, np.uint32)
@@ -127,6 +149,13 @@ def test_shard_ranges_cover_everything():
             assert pos == total
     with pytest.raises(ValueError):
         sh.shard_range(10, 2, 2)
+
+
+def test_chain_owners():
+    import ctg.sharding as sh
+    assert sh.chain_owners(1) == [0, 0, 0] and sh.chain_owners(2) == [0, 1, 0] and sh.chain_owners(8) == [0, 1, 2]
+    assert [sh.chain_mask(r, 2) for r in range(2)] == [0b101, 0b010]
+    assert [sh.chain_mask(r, 8) for r in range(8)] == [1, 2, 4, 0, 0, 0, 0, 0]
 
 
 def test_two_rank_sharded_proof_over_gloo():
