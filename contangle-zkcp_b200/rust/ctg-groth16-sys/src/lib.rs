@@ -16,6 +16,7 @@ pub const CTG_MSM_TIMED: u32 = 0x100;
 #[repr(C)] pub struct ctg_bases { _p: [u8; 0] }
 #[repr(C)] pub struct ctg_pk { _p: [u8; 0] }
 #[repr(C)] pub struct ctg_r1cs { _p: [u8; 0] }
+#[repr(C)] pub struct ctg_params { _p: [u8; 0] }
 
 /// ark-ff Fp256 memory image: [u64; 4] little-endian Montgomery limbs == [u32; 8]
 #[repr(C)] #[derive(Clone, Copy, Default)] pub struct ctg_fr { pub v: [u32; 8] }
@@ -37,6 +38,17 @@ pub struct ctg_pk_view {
     pub h_query: *const ctg_g1_affine, pub h_len: u64,
     pub l_query: *const ctg_g1_affine, pub l_len: u64,
 }
+/// trapdoor of ark_groth16::generate_parameters, drawn by the caller in arkworks' order
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct ctg_trapdoor { pub alpha: ctg_fr, pub beta: ctg_fr, pub gamma: ctg_fr, pub delta: ctg_fr, pub tau: ctg_fr, pub g1: ctg_g1_affine, pub g2: ctg_g2_affine }
+#[repr(C)]
+pub struct ctg_params_out {
+    pub alpha_g1: *mut ctg_g1_affine, pub beta_g1: *mut ctg_g1_affine, pub delta_g1: *mut ctg_g1_affine,
+    pub beta_g2: *mut ctg_g2_affine, pub gamma_g2: *mut ctg_g2_affine, pub delta_g2: *mut ctg_g2_affine,
+    pub gamma_abc_g1: *mut ctg_g1_affine, pub a_query: *mut ctg_g1_affine, pub b_g1_query: *mut ctg_g1_affine,
+    pub b_g2_query: *mut ctg_g2_affine, pub h_query: *mut ctg_g1_affine, pub l_query: *mut ctg_g1_affine,
+}
+#[repr(C)] #[derive(Clone, Copy)] pub struct ctg_proof_partial { pub a: ctg_g1_xyzz, pub b1: ctg_g1_xyzz, pub l: ctg_g1_xyzz, pub h: ctg_g1_xyzz, pub b2: ctg_g2_xyzz }
 #[repr(C)] pub struct ctg_csr { pub row_ptr: *const u64, pub col: *const u32, pub val: *const ctg_fr }
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct ctg_timings {
@@ -68,4 +80,29 @@ extern "C" {
                      out: *mut ctg_proof, timings: *mut ctg_timings) -> i32;
     pub fn ctg_prove_batch(ctx: *mut ctg_ctx, pk: *const ctg_pk, r1cs: *const ctg_r1cs, n_proofs: u32, z_batch: *const ctg_fr,
                            rs_batch: *const ctg_fr, out: *mut ctg_proof) -> i32;
+    // multi-GPU: point-range key shards, partial sums, distributed witness map
+    pub fn ctg_pk_upload_shard(ctx: *mut ctg_ctx, pk: *const ctg_pk_view, num_instance: u64, num_constraints: u64, copies: c_int, c_bits: c_int,
+                               shard_index: c_int, shard_count: c_int, out: *mut *mut ctg_pk) -> i32;
+    pub fn ctg_prove_partial(ctx: *mut ctg_ctx, pk: *const ctg_pk, r1cs: *const ctg_r1cs, z: *const ctg_fr, r: *const ctg_fr, s: *const ctg_fr,
+                             out: *mut ctg_proof_partial, timings: *mut ctg_timings) -> i32;
+    pub fn ctg_prove_partial_begin(ctx: *mut ctg_ctx, pk: *const ctg_pk, r1cs: *const ctg_r1cs, z: *const ctg_fr, r: *const ctg_fr, s: *const ctg_fr,
+                                   chain_mask: u32, d_abc: *mut c_void) -> i32;
+    pub fn ctg_prove_partial_finish(ctx: *mut ctg_ctx, pk: *const ctg_pk, r1cs: *const ctg_r1cs, r: *const ctg_fr, s: *const ctg_fr,
+                                    d_abc: *mut c_void, out: *mut ctg_proof_partial) -> i32;
+    pub fn ctg_prove_combine(ctx: *mut ctg_ctx, partials: *const ctg_proof_partial, k: u32, r: *const ctg_fr, s: *const ctg_fr, out: *mut ctg_proof) -> i32;
+    // verifier-side aggregation, key generation, wire formats
+    pub fn ctg_prepare_inputs(ctx: *mut ctg_ctx, gamma_abc_g1: *const ctg_bases, public_inputs: *const ctg_fr, n_inputs: u64, out: *mut ctg_g1_affine) -> i32;
+    pub fn ctg_generate_parameters(ctx: *mut ctg_ctx, num_instance: u64, num_witness: u64, num_constraints: u64, a: *const ctg_csr, b: *const ctg_csr,
+                                   c: *const ctg_csr, trapdoor: *const ctg_trapdoor, out: *mut *mut ctg_params) -> i32;
+    pub fn ctg_params_pk_view(ctx: *mut ctg_ctx, params: *const ctg_params, out: *mut ctg_pk_view, gamma_abc_g1: *mut *const ctg_g1_affine,
+                              gamma_abc_len: *mut u64) -> i32;
+    pub fn ctg_params_download(ctx: *mut ctg_ctx, params: *const ctg_params, dst: *const ctg_params_out) -> i32;
+    pub fn ctg_params_free(ctx: *mut ctg_ctx, params: *mut ctg_params);
+    pub fn ctg_params_deserialize_unchecked(ctx: *mut ctg_ctx, key_image: *const u8, len: u64, out: *mut *mut ctg_params) -> i32;
+    pub fn ctg_params_serialize_unchecked(ctx: *mut ctg_ctx, params: *const ctg_params, out: *mut u8, capacity: u64, written: *mut u64) -> i32;
+    pub fn ctg_params_serialize_vk(ctx: *mut ctg_ctx, params: *const ctg_params, out: *mut u8, capacity: u64, written: *mut u64) -> i32;
+    pub fn ctg_proof_serialize(proof: *const ctg_proof, out192: *mut u8) -> i32;
+    pub fn ctg_proof_deserialize(in192: *const u8, check_subgroup: c_int, out: *mut ctg_proof) -> i32;
+    pub fn ctg_host_alloc(ctx: *mut ctg_ctx, bytes: usize, h_out: *mut *mut c_void) -> i32;
+    pub fn ctg_host_free(ctx: *mut ctg_ctx, h_ptr: *mut c_void) -> i32;
 }

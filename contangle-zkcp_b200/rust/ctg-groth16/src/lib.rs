@@ -57,6 +57,62 @@ impl<'c> DeviceProvingKey<'c> {
         Ok(Self { ctx, pk: raw, r1cs: Mutex::new(None), vk: pk.vk.clone(), num_instance, num_constraints })
     }
 }
+impl<'c> DeviceProvingKey<'c> {
+    /// `read_proving_key` (reference: lib/src/utils.rs:104-110) without the host-side ProvingKey: the circuit.zkey image
+    /// (ProvingKey::serialize_unchecked) is decoded on the device.  `vk` comes from verification.key as before.
+    pub fn from_zkey_bytes(ctx: &'c Context, image: &[u8], vk: VerifyingKey<Bls12_381>, num_constraints: usize) -> Result<Self, SynthesisError> {
+        let g = ctx.raw.lock().unwrap();
+        let (mut params, mut raw) = (ptr::null_mut(), ptr::null_mut());
+        if unsafe { sys::ctg_params_deserialize_unchecked(*g, image.as_ptr(), image.len() as u64, &mut params) } != sys::CTG_OK {
+            return Err(SynthesisError::MalformedVerifyingKey)
+        }
+        let num_instance = vk.gamma_abc_g1.len();
+        let mut view = std::mem::MaybeUninit::<sys::ctg_pk_view>::uninit();
+        let rc = unsafe {
+            sys::ctg_params_pk_view(*g, params, view.as_mut_ptr(), ptr::null_mut(), ptr::null_mut());
+            let rc = sys::ctg_pk_upload(*g, view.as_ptr(), num_instance as u64, num_constraints as u64, 0, 0, &mut raw); // device to device
+            sys::ctg_params_free(*g, params);
+            rc
+        };
+        if rc != sys::CTG_OK { return Err(SynthesisError::MalformedVerifyingKey) }
+        Ok(Self { ctx, pk: raw, r1cs: Mutex::new(None), vk, num_instance, num_constraints })
+    }
+}
+
+/// ark_groth16::generate_random_parameters with the arithmetic on the device (ctg_generate_parameters).  The trapdoor is
+/// drawn here in ark-groth16 0.3.0's order so the RNG stream matches generator.rs: alpha, beta, gamma, delta,
+/// G1Projective::rand, G2Projective::rand, then tau = domain.sample_element_outside_domain(rng) after Setup-mode synthesis.
+/// Returns the host ProvingKey (downloaded once, for `write_circuit_artifacts`) -- or keep the handle and call
+/// `ctg_params_serialize_unchecked` to write circuit.zkey without materialising it on the host.
+pub fn generate_random_parameters<C, R>(ctx: &Context, circuit: C, rng: &mut R) -> Result<ProvingKey<Bls12_381>, SynthesisError>
+where C: ConstraintSynthesizer<Fr>, R: RngCore + CryptoRng {
+    use ark_bls12_381::{G1Projective, G2Projective};
+    use ark_ec::ProjectiveCurve;
+    use ark_poly::{EvaluationDomain, GeneralEvaluationDomain};
+    let (alpha, beta, gamma, delta) = (Fr::rand(rng), Fr::rand(rng), Fr::rand(rng), Fr::rand(rng));
+    let (g1, g2) = (G1Projective::rand(rng).into_affine(), G2Projective::rand(rng).into_affine());
+    let cs = ConstraintSystem::new_ref();
+    cs.set_optimization_goal(OptimizationGoal::Constraints);
+    cs.set_mode(ark_relations::r1cs::SynthesisMode::Setup);
+    circuit.generate_constraints(cs.clone())?;
+    cs.finalize();
+    let (ni, nw, nc) = (cs.num_instance_variables(), cs.num_witness_variables(), cs.num_constraints());
+    let domain = GeneralEvaluationDomain::<Fr>::new(nc + ni).ok_or(SynthesisError::PolynomialDegreeTooLarge)?;
+    let tau = domain.sample_element_outside_domain(rng);
+    let m = cs.to_matrices().ok_or(SynthesisError::AssignmentMissing)?;
+    let (a, b, c) = (pack::Csr::from_rows(&m.a), pack::Csr::from_rows(&m.b), pack::Csr::from_rows(&m.c));
+    let td = sys::ctg_trapdoor { alpha: pack::fr_image(&alpha), beta: pack::fr_image(&beta), gamma: pack::fr_image(&gamma),
+                                 delta: pack::fr_image(&delta), tau: pack::fr_image(&tau), g1: pack::g1_image(&g1), g2: pack::g2_image(&g2) };
+    let g = ctx.raw.lock().unwrap();
+    let mut params = ptr::null_mut();
+    if unsafe { sys::ctg_generate_parameters(*g, ni as u64, nw as u64, nc as u64, &a.view(), &b.view(), &c.view(), &td, &mut params) } != sys::CTG_OK {
+        return Err(SynthesisError::Unsatisfiable)
+    }
+    let pk = pack::download_pk(*g, params, ni, nw, domain.size());   // ctg_params_download into Vec<G1Affine> / Vec<G2Affine>
+    unsafe { sys::ctg_params_free(*g, params) };
+    pk
+}
+
 impl<'c> Drop for DeviceProvingKey<'c> {
     fn drop(&mut self) {
         let g = self.ctx.raw.lock().unwrap();

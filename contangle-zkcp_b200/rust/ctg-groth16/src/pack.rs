@@ -81,3 +81,24 @@ impl Csr {
     pub fn view(&self) -> sys::ctg_csr { sys::ctg_csr { row_ptr: self.row_ptr.as_ptr(), col: self.col.as_ptr(), val: self.val.as_ptr() } }
 }
 #[allow(dead_code)] fn _assert_layout(_: Fp256<ark_bls12_381::FrParameters>) {}
+
+/// ctg_params_download -> ark_groth16::ProvingKey (used by `generate_random_parameters`)
+pub fn download_pk(ctx: *mut sys::ctg_ctx, params: *const sys::ctg_params, ni: usize, nw: usize, n: usize)
+    -> Result<ProvingKey<Bls12_381>, ark_relations::r1cs::SynthesisError> {
+    let m = ni + nw;
+    let z1 = sys::ctg_g1_affine { x: ZQ, y: ZQ };
+    let z2 = sys::ctg_g2_affine { x_c0: ZQ, x_c1: ZQ, y_c0: ZQ, y_c1: ZQ };
+    let (mut s1, mut s2) = ([z1; 3], [z2; 3]);
+    let (mut abc, mut a, mut b1, mut b2, mut h, mut l) = (vec![z1; ni], vec![z1; m], vec![z1; m], vec![z2; m], vec![z1; n - 1], vec![z1; nw]);
+    let dst = sys::ctg_params_out {
+        alpha_g1: &mut s1[0], beta_g1: &mut s1[1], delta_g1: &mut s1[2], beta_g2: &mut s2[0], gamma_g2: &mut s2[1], delta_g2: &mut s2[2],
+        gamma_abc_g1: abc.as_mut_ptr(), a_query: a.as_mut_ptr(), b_g1_query: b1.as_mut_ptr(), b_g2_query: b2.as_mut_ptr(),
+        h_query: h.as_mut_ptr(), l_query: l.as_mut_ptr(),
+    };
+    if unsafe { sys::ctg_params_download(ctx, params, &dst) } != sys::CTG_OK { return Err(ark_relations::r1cs::SynthesisError::Unsatisfiable) }
+    let vk = ark_groth16::VerifyingKey { alpha_g1: g1_from(&s1[0]), beta_g2: g2_from(&s2[0]), gamma_g2: g2_from(&s2[1]), delta_g2: g2_from(&s2[2]),
+                                         gamma_abc_g1: abc.iter().map(g1_from).collect() };
+    Ok(ProvingKey { vk, beta_g1: g1_from(&s1[1]), delta_g1: g1_from(&s1[2]), a_query: a.iter().map(g1_from).collect(),
+                    b_g1_query: b1.iter().map(g1_from).collect(), b_g2_query: b2.iter().map(g2_from).collect(),
+                    h_query: h.iter().map(g1_from).collect(), l_query: l.iter().map(g1_from).collect() })
+}
