@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libctg_groth16.so")
+LIB_PATH = os.environ.get("CTG_LIB") or os.path.join(os.path.dirname(_HERE), "libctg_groth16.so")   # CTG_LIB: alternative builds in kernel sweeps
 
 FR_W, FQ_W, G1_W, G2_W = 8, 12, 24, 48
 PARTIAL_W = 4 * 2 * G1_W + 2 * G2_W   # ctg_proof_partial: 4 G1 XYZZ + 1 G2 XYZZ = 288 words (1152 B)

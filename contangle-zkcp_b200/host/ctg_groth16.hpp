@@ -9,6 +9,9 @@
 //   ark_groth16::create_proof(circuit, pk, r, s) -> ctg::create_proof(dpk, cs, r, s)
 //   ark_groth16::create_random_proof(.., rng)    -> ctg::create_random_proof(dpk, cs, rng)   (r first, then s)
 //   ark_groth16::Proof<Bls12_381>                -> ctg::Proof { a, b, c }
+//   ark_groth16::generate_parameters(..)         -> ctg::generate_parameters(ctx, cs, trapdoor) -> ctg::DeviceParams
+//   read_proving_key (lib/src/utils.rs:104-110)  -> ctg::read_proving_key(ctx, circuit.zkey bytes)  -> ctg::DeviceParams
+//   ark_to_bytes(proof) / ark_from_bytes         -> ctg::proof_to_bytes / ctg::proof_from_bytes   (192 compressed bytes)
 //   SynthesisError                               -> ctg::Error (std::runtime_error with the C ABI message)
 //
 // "cs" is the synthesized constraint system (matrices + full assignment): synthesis itself is circuit code and
@@ -69,8 +72,77 @@ struct ConstraintSystem {
   size_t num_constraints() const { return a.size(); }
 };
 
+// CSR views of a ConstraintSystem's three matrices (storage lives in the object)
+struct FlatMatrices {
+  struct Flat { std::vector<uint64_t> rp; std::vector<uint32_t> col; std::vector<ctg_fr> val; ctg_csr view; };
+  Flat f[3];
+  explicit FlatMatrices(const ConstraintSystem& cs) {
+    const std::vector<Row>* mats[3] = {&cs.a, &cs.b, &cs.c};
+    for (int k = 0; k < 3; k++) {
+      f[k].rp.push_back(0);
+      for (const Row& row : *mats[k]) {
+        for (const auto& e : row) { f[k].val.push_back(e.first); f[k].col.push_back((uint32_t)e.second); }
+        f[k].rp.push_back(f[k].col.size());
+      }
+      f[k].view = ctg_csr{f[k].rp.data(), f[k].col.data(), f[k].val.data()};
+    }
+  }
+};
+
+// A Groth16 key resident in HBM in arkworks' order (ctg_params): the output of key generation or of reading circuit.zkey.
+class DeviceParams {
+ public:
+  DeviceParams(const Context& ctx, ctg_params* p) : ctx_(ctx), p_(p) {}
+  ~DeviceParams() { ctg_params_free(ctx_.raw(), p_); }
+  DeviceParams(const DeviceParams&) = delete;
+  DeviceParams& operator=(const DeviceParams&) = delete;
+  const Context& ctx() const { return ctx_; }
+  const ctg_params* raw() const { return p_; }
+  ctg_pk_view view(uint64_t* num_instance = nullptr) const {
+    ctg_pk_view v{};
+    ctx_.check(ctg_params_pk_view(ctx_.raw(), p_, &v, nullptr, num_instance));
+    return v;
+  }
+  // ProvingKey::serialize_unchecked (circuit.zkey) and VerifyingKey::serialize (verification.key): write_circuit_artifacts
+  std::vector<uint8_t> serialize_unchecked() const { return ser(ctg_params_serialize_unchecked); }
+  std::vector<uint8_t> serialize_vk() const { return ser(ctg_params_serialize_vk); }
+
+ private:
+  template <class Fn> std::vector<uint8_t> ser(Fn fn) const {
+    uint64_t n = 0;
+    ctx_.check(fn(ctx_.raw(), p_, nullptr, 0, &n));
+    std::vector<uint8_t> out(n);
+    ctx_.check(fn(ctx_.raw(), p_, out.data(), n, &n));
+    return out;
+  }
+  const Context& ctx_;
+  ctg_params* p_;
+};
+
+// ark_groth16::generate_parameters after Setup-mode synthesis; the trapdoor is drawn by the caller in arkworks' order
+inline std::unique_ptr<DeviceParams> generate_parameters(const Context& ctx, const ConstraintSystem& cs, const ctg_trapdoor& trapdoor) {
+  FlatMatrices m(cs);
+  ctg_params* p = nullptr;
+  ctx.check(ctg_generate_parameters(ctx.raw(), cs.num_instance_variables, cs.num_witness_variables, cs.num_constraints(), &m.f[0].view, &m.f[1].view,
+                                    &m.f[2].view, &trapdoor, &p));
+  return std::make_unique<DeviceParams>(ctx, p);
+}
+// read_proving_key: ProvingKey::deserialize_unchecked of a circuit.zkey image, decoded on the device
+inline std::unique_ptr<DeviceParams> read_proving_key(const Context& ctx, const std::vector<uint8_t>& image) {
+  ctg_params* p = nullptr;
+  ctx.check(ctg_params_deserialize_unchecked(ctx.raw(), image.data(), image.size(), &p));
+  return std::make_unique<DeviceParams>(ctx, p);
+}
+
 class DeviceProvingKey {
  public:
+  // from a key already in HBM (device-to-device)
+  DeviceProvingKey(const DeviceParams& params, size_t num_constraints, int copies = 0, int c_bits = 0) : ctx_(params.ctx()), nc_(num_constraints) {
+    uint64_t ni = 0;
+    ctg_pk_view v = params.view(&ni);
+    ni_ = ni;
+    ctx_.check(ctg_pk_upload(ctx_.raw(), &v, ni, num_constraints, copies, c_bits, &pk_));
+  }
   // num_instance / num_constraints: shape of the circuit the key was generated for
   DeviceProvingKey(const Context& ctx, const ProvingKey& pk, size_t num_instance, size_t num_constraints, int copies = 0, int c_bits = 0)
       : ctx_(ctx), ni_(num_instance), nc_(num_constraints) {
@@ -95,17 +167,8 @@ class DeviceProvingKey {
   const ctg_r1cs* r1cs_for(const ConstraintSystem& cs) {
     if (cs.num_instance_variables != ni_ || cs.num_constraints() != nc_) throw Error(CTG_ERR_INVALID, "constraint system does not match the proving key");
     if (r1cs_) return r1cs_;
-    struct Flat { std::vector<uint64_t> rp; std::vector<uint32_t> col; std::vector<ctg_fr> val; ctg_csr view; };
-    Flat f[3];
-    const std::vector<Row>* mats[3] = {&cs.a, &cs.b, &cs.c};
-    for (int k = 0; k < 3; k++) {
-      f[k].rp.push_back(0);
-      for (const Row& row : *mats[k]) {
-        for (const auto& e : row) { f[k].val.push_back(e.first); f[k].col.push_back((uint32_t)e.second); }
-        f[k].rp.push_back(f[k].col.size());
-      }
-      f[k].view = ctg_csr{f[k].rp.data(), f[k].col.data(), f[k].val.data()};
-    }
+    FlatMatrices m(cs);
+    auto& f = m.f;
     ctx_.check(ctg_r1cs_upload(ctx_.raw(), cs.num_instance_variables, cs.num_witness_variables, cs.num_constraints(), &f[0].view, &f[1].view,
                                &f[2].view, &r1cs_));
     return r1cs_;
@@ -140,6 +203,20 @@ template <class Rng> inline Proof create_random_proof(DeviceProvingKey& pk, cons
   const ctg_fr r = rng();
   const ctg_fr s = rng();
   return create_proof(pk, cs, r, s);
+}
+
+// ark_to_bytes(proof) / ark_from_bytes::<Proof>: arkworks' compressed canonical form, 48 + 96 + 48 bytes
+inline std::vector<uint8_t> proof_to_bytes(const Proof& p) {
+  ctg_proof raw{p.a, p.b, p.c};
+  std::vector<uint8_t> out(CTG_PROOF_BYTES);
+  if (ctg_proof_serialize(&raw, out.data()) != CTG_OK) throw Error(CTG_ERR_INVALID, "proof_to_bytes");
+  return out;
+}
+inline Proof proof_from_bytes(const std::vector<uint8_t>& bytes, bool check_subgroup = true) {
+  ctg_proof raw;
+  if (bytes.size() != CTG_PROOF_BYTES || ctg_proof_deserialize(bytes.data(), check_subgroup, &raw) != CTG_OK)
+    throw Error(CTG_ERR_INVALID, "SerializationError::InvalidData");
+  return Proof{raw.a, raw.b, raw.c};
 }
 
 }  // namespace ctg
