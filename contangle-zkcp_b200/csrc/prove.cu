@@ -387,10 +387,23 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   auto mark = [&](cudaStream_t st) { if (timed && ne < 16) cudaEventRecord(L.ev_t[ne], st); ne++; };
   if (phase != 2) {
   mark(s0);                                                                   // 0
-  CTG_CUDA(ctx, cudaMemcpyAsync(d_z, z, m * sizeof(Fr), cudaMemcpyHostToDevice, s0));
+  // Upload order: first the part of z this key's A/B1/B2/L MSMs read (for a point-range shard, 1/N of it), so that they start
+  // at once; then the rest, which only the witness map reads -- and only if this rank computes a chain at all.
+  uint64_t s_lo = pk->ext_lo < m ? pk->ext_lo : m, s_hi = pk->ext_lo + pk->ext_cnt < m ? pk->ext_lo + pk->ext_cnt : m;
+  if (pk->l_cnt) {
+    if (pk->ni + pk->l_lo < s_lo) s_lo = pk->ni + pk->l_lo;
+    if (pk->ni + pk->l_lo + pk->l_cnt > s_hi) s_hi = pk->ni + pk->l_lo + pk->l_cnt;
+  }
+  if (s_hi < s_lo) s_hi = s_lo;
+  const ctg_fr* zh = z;
+  if (s_hi > s_lo) CTG_CUDA(ctx, cudaMemcpyAsync(d_z + s_lo, zh + s_lo, (s_hi - s_lo) * sizeof(Fr), cudaMemcpyHostToDevice, s0));
   set_tail_kernel<<<1, 32, 0, s0>>>(d_z, m, r_m, s_m);
   CTG_KERNEL_CHECK(ctx);
   CTG_CUDA(ctx, cudaEventRecord(L.ev_z, s0));
+  if (phase != 1 || chain_mask != 0) {
+    if (s_lo > 0) CTG_CUDA(ctx, cudaMemcpyAsync(d_z, zh, s_lo * sizeof(Fr), cudaMemcpyHostToDevice, s0));
+    if (s_hi < m) CTG_CUDA(ctx, cudaMemcpyAsync(d_z + s_hi, zh + s_hi, (m - s_hi) * sizeof(Fr), cudaMemcpyHostToDevice, s0));
+  }
   mark(s0);                                                                   // 1
   // assignment-only MSMs on their own streams
   struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };

@@ -566,7 +566,7 @@ def test_prove_partial_begin_finish_with_chain_masks(ctx, log_n, shards):
     full.free()
     dev = torch.device("cuda", 0)
     abc = torch.zeros((3, dr.n, 8), dtype=torch.int32, device=dev)
-    whole, stitched = [], []
+    whole, stitched, chainless = [], [], []
     for index in range(shards):
         dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"], shard=(index, shards))
         abc.zero_(); torch.cuda.synchronize()
@@ -585,11 +585,19 @@ def test_prove_partial_begin_finish_with_chain_masks(ctx, log_n, shards):
         assert not bool(abc[0].any()) and bool(abc[1].any()) and bool(abc[2].any())
         abc[0].copy_(a_chain)
         torch.cuda.synchronize()
+        all_chains = abc.clone()
         stitched.append(ctx.prove_partial_finish(dpk, dr, r, s, abc.data_ptr()))
+        # rank "3+": no chain of its own (and only its slice of z is uploaded); everything arrives by broadcast
+        abc.zero_(); torch.cuda.synchronize()
+        ctx.prove_partial_begin(dpk, dr, zm, r, s, 0, abc.data_ptr())
+        assert not bool(abc.any())
+        abc.copy_(all_chains)
+        torch.cuda.synchronize()
+        chainless.append(ctx.prove_partial_finish(dpk, dr, r, s, abc.data_ptr()))
         with pytest.raises(ctg.CtgError):
             ctx.prove_partial_begin(dpk, dr, zm, r, s, 8, abc.data_ptr())
         dpk.free()
-    for parts in (whole, stitched):
+    for parts in (whole, stitched, chainless):
         got = ctx.prove_combine(np.stack(parts), r, s)
         for g, w in zip(got, want):
             assert np.array_equal(g, w)
