@@ -371,7 +371,7 @@ def extras(ctx, torch, dev, stream, S, args):
             row["zkey_load_GBps"] = len(image) / dt / 1e9
             dp2.free()
             del image
-        key_host = dp.download() if lg <= 18 else None
+        key_host = dp.download() if lg <= 20 else None   # CPU-port prove: 2^16, 2^18, 2^20 (about 1 + 3.5 + 13 s on 16 threads)
         dpk = dp.to_device_pk(copies=args.copies)
         dp.free()
         dr = ctx.upload_r1cs(r1cs)

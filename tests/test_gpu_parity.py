@@ -602,3 +602,20 @@ def test_prove_partial_begin_finish_with_chain_masks(ctx, log_n, shards):
         for g, w in zip(got, want):
             assert np.array_equal(g, w)
     dr.free()
+
+
+@pytest.mark.parametrize("log_n", [20])
+def test_prove_full_size_generated_key_closed_form(ctx, log_n):
+    """BASELINE.json configs[2] size (2^20-constraint synthetic R1CS): key GENERATED on the device, proof on the device, and
+    the result pinned by the trapdoor closed form -- three scalar multiplications whose exponents come from O(nnz) big-int
+    arithmetic (tests/util.py: closed_form_proof_arrays), with no MSM / NTT / key oracle in between."""
+    r1cs, zm, z = S.mul_chain(log_n)
+    td_words, td = S.trapdoor(seed=0x5EED + log_n)
+    dp = ctx.generate_parameters(r1cs, td_words)
+    dpk = dp.to_device_pk()
+    dp.free()
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    got = ctx.prove(dpk, dr, zm, fm(r), fm(s))
+    dpk.free(); dr.free()
+    assert util.proof_to_py(got) == util.closed_form_proof_arrays(r1cs, td, z, r, s)

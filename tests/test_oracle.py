@@ -163,3 +163,13 @@ def test_oracle_setup_prove_verify_accepts_and_rejects():
     got = util.trapdoor_pk_arrays(cs, td)
     for k, w in want.items():
         assert np.array_equal(np.asarray(got[k]).reshape(w.shape), w), k
+
+
+def test_closed_form_proof_arrays_matches_bigint_oracle():
+    """tests/util.py's O(nnz) closed form (used at 2^20 on the GPU) against oracle/py's on a small circuit."""
+    from tests import util
+    cs, z = G.mul_chain(4, rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD))
+    td = G.Trapdoor(*[rnd.randrange(1, B.R_MOD) for _ in range(5)], B.G1_GEN, B.G2_GEN)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    got = util.closed_form_proof_arrays(ark.r1cs_from_py(cs), dict(alpha=td.alpha, beta=td.beta, delta=td.delta, tau=td.tau), z, r, s)
+    assert got == G.closed_form_proof(cs, td, z, r, s)

@@ -91,3 +91,43 @@ def cs_from_arrays(r1cs):
             rows.append([(vals[k], int(m["col"][k])) for k in range(lo, hi)])
         setattr(cs, name, rows)
     return cs
+
+
+def closed_form_proof_arrays(r1cs, td, z, r, s, g1=B.G1_GEN, g2=B.G2_GEN):
+    """The Groth16 proof as three scalar multiplications of the generators (SURVEY 8(c) pin 4) for an array-dict R1CS of any
+    size: O(nnz) big-int work, Lagrange coefficients from oracle/c.  td: dict of ints alpha, beta, delta, tau (gamma unused).
+    h(tau) t(tau) comes from the QAP identity A(tau) B(tau) - C(tau), not from any NTT."""
+    R = B.R_MOD
+    ni, nc = r1cs["num_instance"], r1cs["num_constraints"]
+    n = 1
+    while n < ni + nc:
+        n *= 2
+    L = ark.fr_ints_from_mont(ark.lagrange_coeffs(n.bit_length() - 1, ark.fr_mont_from_ints([td["tau"]])[0]))
+    tot, inst = [], []
+    for name in "abc":
+        m = r1cs[name]
+        vals = ark.fr_ints_from_mont(m["val"]) if len(m["col"]) else []
+        cols, rp = m["col"].tolist(), m["row_ptr"].tolist()
+        total, icol = 0, [0] * ni
+        for i in range(nc):
+            Li = L[i]
+            for k in range(rp[i], rp[i + 1]):
+                c = cols[k]
+                t = vals[k] * Li
+                total += t * z[c]
+                if c < ni:
+                    icol[c] += t
+        if name == "a":
+            for j in range(ni):
+                total += L[nc + j] * z[j]
+                icol[j] += L[nc + j]
+        tot.append(total % R)
+        inst.append([x % R for x in icol])
+    az, bz, cz = tot
+    inst_part = sum((td["beta"] * inst[0][j] + td["alpha"] * inst[1][j] + inst[2][j]) * z[j] for j in range(ni)) % R
+    laux = (td["beta"] * az + td["alpha"] * bz + cz - inst_part) % R
+    ht = (az * bz - cz) % R          # h(tau) * t(tau)
+    ea = (td["alpha"] + az + r * td["delta"]) % R
+    eb = (td["beta"] + bz + s * td["delta"]) % R
+    ec = ((laux + ht) * B.fr_inv(td["delta"]) + s * ea + r * eb - r * s % R * td["delta"]) % R
+    return B.G1.mul(g1, ea), B.G2.mul(g2, eb), B.G1.mul(g1, ec)
