@@ -285,12 +285,49 @@ def main():
                                 "gpu_matches_cpu_on_sample": bool(np.array_equal(cpu_pt, gpu_pt))}
         if not args.no_extras:
             line["extra"] = extras(ctx, torch, dev, stream, S, args)
+    if world > 1 and not args.no_extras:
+        ex = extras_sharded(ctx, torch, dev, S, dist, rank, world)     # every rank takes part
+        if rank == 0:
+            line["extra"] = ex
     if rank == 0:
         print(json.dumps(line), file=OUT, flush=True)
     bases.free()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def extras_sharded(ctx, torch, dev, S, dist, rank, world):
+    """BASELINE.json configs[3] at N > 1: one Groth16 proof sharded over the ranks (point-range key shards, NTT chains on their owner
+    ranks and broadcast over NCCL, one all_gather of 1152 B per rank, rank 0 finalises).  Strong scaling: the circuit is fixed."""
+    from ctg import sharding
+    out = {}
+    for lg in (20, 22):
+        r1cs, zm, _ = S.mul_chain(lg)
+        dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])   # the same key on every rank; each keeps its shard
+        dpk = dp.to_device_pk(shard=(rank, world))
+        dp.free()
+        dr = ctx.upload_r1cs(r1cs)
+        zp = ctx.pinned_like(zm)
+        r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
+        for _ in range(2):
+            sharding.sharded_prove(ctx, dpk, dr, zp, r, s, dist, dev)
+        times = []
+        for _ in range(5):
+            dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            sharding.sharded_prove(ctx, dpk, dr, zp, r, s, dist, dev)
+            torch.cuda.synchronize()
+            t = torch.tensor([time.perf_counter() - t0], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            times.append(float(t[0]) * 1e3)
+        times.sort()
+        out[f"groth16_prove_sharded_mulchain_2^{lg}"] = {"n_gpus": world, "wall_ms_median": times[len(times) // 2], "wall_ms_min": times[0],
+                                                         "scaling": "strong", "exchange": "3 broadcasts of n*32 B (NTT chains) + all_gather of 1152 B per rank",
+                                                         "chain_owner_ranks": sharding.chain_owners(world)}
+        ctx.pinned_free(zp)
+        dpk.free(); dr.free()
+    return out
 
 
 def extras(ctx, torch, dev, stream, S, args):
