@@ -178,6 +178,34 @@ __global__ void bitrev_permute_kernel(Fr* data, int log_n) {
   }
 }
 
+// Tiled bit-reversal permutation for log_n >= 8.  Index i = (h : 4 bits | m : log_n - 8 bits | l : 4 bits) maps to
+// (rev l | rev m | rev h): the 16 x 16 tile of all (h, l) for one m lands on the tile of rev m, transposed.  One CTA swaps
+// the pair (m, rev m) through shared memory, so both the loads and the stores are runs of 16 consecutive elements (512 B)
+// instead of single scattered 32-byte sectors.
+__global__ void __launch_bounds__(256) bitrev_tiled_kernel(Fr* data, int log_n) {
+  __shared__ uint4 tile[2][16][17][2];   // row stride 17 elements = 136 words: rows fall into distinct bank groups
+  const int mid_bits = log_n - 8;
+  const uint32_t m = blockIdx.x;
+  const uint32_t rm = mid_bits ? (__brev(m) >> (32 - mid_bits)) : 0u;
+  if (m > rm) return;
+  const int r = threadIdx.x >> 4, c = threadIdx.x & 15;
+  const int rr = __brev((uint32_t)r) >> 28, rc = __brev((uint32_t)c) >> 28;
+  const uint64_t ia = ((uint64_t)r << (log_n - 4)) | ((uint64_t)m << 4) | (uint64_t)c;
+  const uint64_t ib = ((uint64_t)r << (log_n - 4)) | ((uint64_t)rm << 4) | (uint64_t)c;
+  uint4* pa = reinterpret_cast<uint4*>(data + ia);
+  uint4* pb = reinterpret_cast<uint4*>(data + ib);
+  tile[0][r][c][0] = pa[0]; tile[0][r][c][1] = pa[1];
+  if (m != rm) { tile[1][r][c][0] = pb[0]; tile[1][r][c][1] = pb[1]; }
+  __syncthreads();
+  // position (h' = r, l' = c) of the destination tile holds source (h = rev c, l = rev r)
+  if (m != rm) {
+    pb[0] = tile[0][rc][rr][0]; pb[1] = tile[0][rc][rr][1];
+    pa[0] = tile[1][rc][rr][0]; pa[1] = tile[1][rc][rr][1];
+  } else {
+    pa[0] = tile[0][rc][rr][0]; pa[1] = tile[0][rc][rr][1];
+  }
+}
+
 __global__ void scale_table_kernel(Fr* data, uint64_t n, const Fr* tab, Fr c, int use_c) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -323,7 +351,8 @@ int32_t ntt_run(ctg_ctx* ctx, Fr* d, int log_n, int inverse, int coset, cudaStre
   }
   if (log_n > 1) {
     uint64_t n = 1ull << log_n;
-    bitrev_permute_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, log_n);
+    if (log_n >= 8) bitrev_tiled_kernel<<<(unsigned)(n >> 8), 256, 0, st>>>(d, log_n);
+    else bitrev_permute_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, log_n);
     CTG_KERNEL_CHECK(ctx);
   }
   return CTG_OK;

@@ -619,3 +619,32 @@ def test_prove_full_size_generated_key_closed_form(ctx, log_n):
     got = ctx.prove(dpk, dr, zm, fm(r), fm(s))
     dpk.free(); dr.free()
     assert util.proof_to_py(got) == util.closed_form_proof_arrays(r1cs, td, z, r, s)
+
+
+def test_setup_prove_verify_circuit_without_witnesses(ctx):
+    """Edge case: every variable is public (num_witness = 0), so l_query is empty and the L MSM has no points; one constraint
+    row is empty in C.  Setup and prove on the device against oracle/py, then the pairing equation."""
+    from oracle.py import pairing as PR
+    cs = G.R1CS(num_instance=3, num_witness=0)           # z = (1, x, y):  x * x = y,  (x - 3) * 0 = 0
+    cs.a = [[(1, 1)], [(1, 1), (B.R_MOD - 3, 0)]]
+    cs.b = [[(1, 1)], []]
+    cs.c = [[(1, 2)], []]
+    z = [1, 3, 9]
+    assert cs.is_satisfied(z)
+    td = _trapdoor()
+    r1 = ark.r1cs_from_py(cs)
+    want_pk = G.generate_parameters(cs, td)
+    dp = ctx.generate_parameters(r1, util.trapdoor_words(td))
+    got = dp.download()
+    for k, w in ark.pk_from_py(want_pk).items():
+        assert np.array_equal(got[k].reshape(w.shape), w), k
+    assert got["l_query"].shape == (0, 24)
+    dpk, dr = dp.to_device_pk(), ctx.upload_r1cs(r1)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    proof = util.proof_to_py(ctx.prove(dpk, dr, ark.fr_mont_from_ints(z), fm(r), fm(s)))
+    assert proof == G.create_proof(cs, want_pk, z, r, s)
+    assert PR.groth16_verify(want_pk.alpha_g1, want_pk.beta_g2, want_pk.gamma_g2, want_pk.delta_g2, want_pk.gamma_abc_g1, proof, z[1:])
+    image = dp.serialize_unchecked()
+    dp2 = ctx.load_proving_key(image)
+    assert dp2.serialize_unchecked() == image and (dp2.ni, dp2.nw) == (3, 0)
+    dp2.free(); dpk.free(); dr.free(); dp.free()
