@@ -150,7 +150,7 @@ static int32_t make_bases(ctg_ctx* ctx, Bases& out, int group, uint64_t n, int c
   CTG_CUDA(ctx, cudaMemsetAsync(out.pts, 0, bytes, ctx->stream));
   return CTG_OK;
 }
-static int32_t finish_bases(ctg_ctx* ctx, Bases& b) { return b.group == 1 ? g1_precompute(ctx, b, ctx->stream) : g2_precompute(ctx, b, ctx->stream); }
+static int32_t finish_bases(ctg_ctx* ctx, Bases& b) { if (b.n == 0) return CTG_OK;  /* an empty query (e.g. l_query of a circuit without witnesses) */ return b.group == 1 ? g1_precompute(ctx, b, ctx->stream) : g2_precompute(ctx, b, ctx->stream); }
 
 // positions [lo, lo + cnt) of (query ++ extras[0..3)) -> dst; extras may hold nullptr (= point at infinity, dst is pre-zeroed)
 template <class A>
