@@ -648,3 +648,30 @@ def test_setup_prove_verify_circuit_without_witnesses(ctx):
     dp2 = ctx.load_proving_key(image)
     assert dp2.serialize_unchecked() == image and (dp2.ni, dp2.nw) == (3, 0)
     dp2.free(); dpk.free(); dr.free(); dp.free()
+
+
+@pytest.mark.parametrize("shape", ["n1-empty", "n2-one-constraint", "n4-ragged"])
+def test_setup_prove_tiny_domains(ctx, shape):
+    """Smallest domains (n = 1, 2, 4): empty h_query (n - 1 = 0), no constraints at all, and a domain that the constraint count
+    does not fill (zero padding rows).  Key and proof against oracle/py."""
+    if shape == "n1-empty":
+        cs, z = G.R1CS(num_instance=1, num_witness=0), [1]
+    elif shape == "n2-one-constraint":
+        cs, z = G.R1CS(num_instance=1, num_witness=1), [1, 1]
+        cs.a, cs.b, cs.c = [[(1, 1)]], [[(1, 1)]], [[(1, 1)]]          # w * w = w
+    else:
+        cs, z = G.R1CS(num_instance=2, num_witness=1), [1, 25, 5]      # n = next_pow2(1 + 2) = 4, one padding row
+        cs.a, cs.b, cs.c = [[(1, 2)]], [[(1, 2)]], [[(1, 1)]]          # w * w = x
+    assert cs.is_satisfied(z)
+    td = _trapdoor()
+    r1 = ark.r1cs_from_py(cs)
+    want_pk = G.generate_parameters(cs, td)
+    dp = ctx.generate_parameters(r1, util.trapdoor_words(td))
+    got = dp.download()
+    for k, w in ark.pk_from_py(want_pk).items():
+        assert np.array_equal(got[k].reshape(w.shape), w), k
+    dpk, dr = dp.to_device_pk(), ctx.upload_r1cs(r1)
+    r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
+    proof = util.proof_to_py(ctx.prove(dpk, dr, ark.fr_mont_from_ints(z), fm(r), fm(s)))
+    assert proof == G.create_proof(cs, want_pk, z, r, s)
+    dpk.free(); dr.free(); dp.free()
