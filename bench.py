@@ -327,6 +327,25 @@ def extras_sharded(ctx, torch, dev, S, dist, rank, world):
                                                          "chain_owner_ranks": sharding.chain_owners(world)}
         ctx.pinned_free(zp)
         dpk.free(); dr.free()
+    # BASELINE.json configs[4]: batched PoE-shaped proofs, replicas (key + R1CS on every GPU, independent witnesses per rank, no collective)
+    for n_data in (1, 100):
+        r1cs, zm, _ = S.poe_shape(n_data)
+        dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
+        dpk = dp.to_device_pk()
+        dp.free()
+        dr = ctx.upload_r1cs(r1cs)
+        nb = 32
+        zb = np.ascontiguousarray(np.broadcast_to(zm, (nb,) + zm.shape))
+        rs = np.ascontiguousarray(np.broadcast_to(np.stack([S.fr_mont([3 + rank])[0], S.fr_mont([5])[0]]), (nb, 2, 8)))
+        ctx.prove_batch(dpk, dr, zb, rs)
+        dist.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ctx.prove_batch(dpk, dr, zb, rs)
+        t = torch.tensor([time.perf_counter() - t0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[f"batched_poe_shape_{n_data}_replicas"] = {"n_gpus": world, "domain": S.domain_size(r1cs), "proofs": nb * world,
+                                                       "proofs_per_s": nb * world / float(t[0]), "scaling": "weak (replicas, no collective)"}
+        dpk.free(); dr.free()
     return out
 
 
