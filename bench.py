@@ -305,7 +305,7 @@ def extras_sharded(ctx, torch, dev, S, dist, rank, world):
     for lg in (20, 22):
         r1cs, zm, _ = S.mul_chain(lg)
         dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])   # the same key on every rank; each keeps its shard
-        dpk = dp.to_device_pk(shard=(rank, world))
+        dpk = dp.to_device_pk(shard=sharding.shard_bounds(rank, world))   # weighted: NTT-chain owners keep fewer points
         dp.free()
         dr = ctx.upload_r1cs(r1cs)
         zp = ctx.pinned_like(zm)

@@ -13,7 +13,7 @@ namespace ctg {
 int32_t field_op_dev(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n, cudaStream_t st);
 size_t field_elem_bytes(int field);
 int32_t imad_probe(ctg_ctx* ctx, double* imad_per_s, double* fq_mul_per_s);
-int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, int shard_index, int shard_count, ctg_pk** out);
+int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, uint64_t lo_num, uint64_t hi_num, uint64_t den, ctg_pk** out);
 int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch, ctg_proof* out);
 int32_t prove_partial(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, void* out_partials, ctg_timings* tm);
 int32_t prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, uint32_t chain_mask, void* d_abc);
@@ -452,13 +452,20 @@ int32_t ctg_g2_combine(ctg_ctx* ctx, const ctg_g2_xyzz* host_partials, uint32_t 
 int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits, ctg_pk** out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
   if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 21]");
-  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, 0, 1, out);
+  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, 0, 1, 1, out);
 }
 int32_t ctg_pk_upload_shard(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
                             int shard_index, int shard_count, ctg_pk** out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
   if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 21]");
-  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, shard_index, shard_count, out);
+  if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(ctx, CTG_ERR_INVALID, "pk_upload: bad shard index / count");
+  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, (uint64_t)shard_index, (uint64_t)shard_index + 1, (uint64_t)shard_count, out);
+}
+int32_t ctg_pk_upload_range(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
+                            uint64_t lo_num, uint64_t hi_num, uint64_t den, ctg_pk** out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 21]");
+  return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, lo_num, hi_num, den, out);
 }
 void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk) {
   if (ctx) cudaStreamSynchronize(ctx->stream);

@@ -171,15 +171,18 @@ static cudaError_t upload_ext_range(A* dst, const A* query, uint64_t m, const A*
   return cudaSuccess;
 }
 
-static void shard_range(uint64_t total, int index, int count, uint64_t* lo, uint64_t* cnt) {
-  const uint64_t a = total * (uint64_t)index / (uint64_t)count, b = total * (uint64_t)(index + 1) / (uint64_t)count;
+// positions [total * lo_num / den, total * hi_num / den) -- equal shards are (index, index + 1, count); weighted shards pass
+// cumulative weights, so that ranks which also run NTT chains can take fewer points
+static void shard_range(uint64_t total, uint64_t lo_num, uint64_t hi_num, uint64_t den, uint64_t* lo, uint64_t* cnt) {
+  const uint64_t a = (uint64_t)((unsigned __int128)total * lo_num / den), b = (uint64_t)((unsigned __int128)total * hi_num / den);
   *lo = a;
   *cnt = b - a;
 }
 
-int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, int shard_index, int shard_count, ctg_pk** out) {
+int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, uint64_t lo_num, uint64_t hi_num, uint64_t den, ctg_pk** out) {
   if (!v || !out) return fail(ctx, CTG_ERR_INVALID, "pk_upload: null argument");
-  if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(ctx, CTG_ERR_INVALID, "pk_upload: bad shard index / count");
+  if (den < 1 || lo_num > hi_num || hi_num > den) return fail(ctx, CTG_ERR_INVALID, "pk_upload: bad shard range (need 0 <= lo <= hi <= den, den >= 1)");
+  const int shard_index = lo_num == 0 ? 0 : 1, shard_count = (lo_num == 0 && hi_num == den) ? 1 : 2;   // only "whole key or not" matters downstream
   const uint64_t m = v->a_len;
   if (m < ni || m == 0 || v->b_g1_len != m || v->b_g2_len != m) return fail(ctx, CTG_ERR_INVALID, "pk_upload: a/b query lengths must equal num_instance + num_witness");
   const uint64_t nw = m - ni;
@@ -190,9 +193,9 @@ int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, 
   ctg_pk* pk = new ctg_pk();
   pk->m = m; pk->ni = ni; pk->nw = nw; pk->n = n; pk->log_n = log_n;
   pk->shard_index = shard_index; pk->shard_count = shard_count;
-  shard_range(m + 3, shard_index, shard_count, &pk->ext_lo, &pk->ext_cnt);
-  shard_range(nw, shard_index, shard_count, &pk->l_lo, &pk->l_cnt);
-  shard_range(n, shard_index, shard_count, &pk->h_lo, &pk->h_cnt);
+  shard_range(m + 3, lo_num, hi_num, den, &pk->ext_lo, &pk->ext_cnt);
+  shard_range(nw, lo_num, hi_num, den, &pk->l_lo, &pk->l_cnt);
+  shard_range(n, lo_num, hi_num, den, &pk->h_lo, &pk->h_cnt);
   cudaStream_t st = ctx->stream;
   auto cleanup = [&](int32_t rc) { free_bases(pk->a_ext); free_bases(pk->b1_ext); free_bases(pk->b2_ext); free_bases(pk->l); free_bases(pk->h_ext); delete pk; return rc; };
   memset(&pk->a_ext, 0, sizeof(Bases)); memset(&pk->b1_ext, 0, sizeof(Bases)); memset(&pk->b2_ext, 0, sizeof(Bases));

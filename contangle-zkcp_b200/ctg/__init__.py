@@ -37,6 +37,7 @@ EXPORTS = [
     "ctg_generate_parameters", "ctg_params_pk_view", "ctg_params_download", "ctg_params_free",
     "ctg_params_deserialize_unchecked", "ctg_params_serialize_unchecked", "ctg_params_serialize_vk",
     "ctg_proof_serialize", "ctg_proof_deserialize", "ctg_prove_partial_begin", "ctg_prove_partial_finish",
+    "ctg_pk_upload_range",
 ]
 
 
@@ -314,13 +315,20 @@ class Context:
         for k, w in (("a_query", G1_W), ("b_g1_query", G1_W), ("b_g2_query", G2_W), ("h_query", G1_W), ("l_query", G1_W)):
             a = _arr(pk[k]).reshape(-1, w); keep.append(a); setattr(v, k, a.ctypes.data)
             setattr(v, k.replace("_query", "_len"), a.shape[0])
+        return DevicePk(self, self._pk_upload(v, num_instance, num_constraints, copies, c_bits, shard), pk["a_query"].shape[0])
+
+    def _pk_upload(self, v, num_instance, num_constraints, copies, c_bits, shard):
+        """shard: None (whole key), (index, count) equal point-range shards, or (lo_num, hi_num, den) a weighted range."""
         h = C.c_void_p()
         if shard is None:
             self._check(load().ctg_pk_upload(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits, C.byref(h)))
-        else:
+        elif len(shard) == 2:
             self._check(load().ctg_pk_upload_shard(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits,
                                                    int(shard[0]), int(shard[1]), C.byref(h)))
-        return DevicePk(self, h, pk["a_query"].shape[0])
+        else:
+            self._check(load().ctg_pk_upload_range(self.h, C.byref(v), C.c_uint64(num_instance), C.c_uint64(num_constraints), copies, c_bits,
+                                                   C.c_uint64(int(shard[0])), C.c_uint64(int(shard[1])), C.c_uint64(int(shard[2])), C.byref(h)))
+        return h
 
     @staticmethod
     def _csr_triplet(r1cs):
@@ -477,13 +485,7 @@ class DeviceParams:
     def to_device_pk(self, copies=0, c_bits=0, shard=None):
         """Device-to-device: build the prover's key cache (ctg_pk) straight from the generated key."""
         v, _, _ = self._view()
-        h = C.c_void_p()
-        if shard is None:
-            self.ctx._check(load().ctg_pk_upload(self.ctx.h, C.byref(v), C.c_uint64(self.ni), C.c_uint64(self.nc), copies, c_bits, C.byref(h)))
-        else:
-            self.ctx._check(load().ctg_pk_upload_shard(self.ctx.h, C.byref(v), C.c_uint64(self.ni), C.c_uint64(self.nc), copies, c_bits,
-                                                       int(shard[0]), int(shard[1]), C.byref(h)))
-        return DevicePk(self.ctx, h, self.ni + self.nw)
+        return DevicePk(self.ctx, self.ctx._pk_upload(v, self.ni, self.nc, copies, c_bits, shard), self.ni + self.nw)
 
     def gamma_abc_bases(self, copies=1, c_bits=0):
         """vk.gamma_abc_g1 as a base table for Context.prepare_inputs (device-to-device)."""

@@ -54,6 +54,38 @@ def chain_mask(rank: int, world: int) -> int:
     return sum(1 << k for k, o in enumerate(chain_owners(world)) if o == rank)
 
 
+SHARD_DEN = 1 << 20
+CHAIN_COST = 0.033   # one NTT chain (SpMV + 2 transforms + the full assignment upload) relative to ALL five MSMs of a proof
+                     # (measured on B200: about 20 ms against 626 ms at 2^24, 5 ms against 147 ms at 2^22)
+
+
+def shard_bounds(rank: int, world: int, distribute_ntt: bool = True, chain_cost: float = CHAIN_COST):
+    """(lo_num, hi_num, den) for ctg_pk_upload_range: the share of every query rank `rank` keeps.  Equal shares when the
+    witness map is replicated; otherwise ranks that own NTT chains get fewer points, so that MSM share + chain work is the
+    same on every rank:  share_i = (1 + 3 c) / N - k_i c  with k_i chains on rank i.  The bounds of all ranks tile [0, den)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("bad rank / world size")
+    if not distribute_ntt or world == 1:
+        return rank * SHARD_DEN // world, (rank + 1) * SHARD_DEN // world, SHARD_DEN
+    owners = chain_owners(world)
+    k = [owners.count(i) for i in range(world)]
+    share = [max((1 + 3 * chain_cost) / world - k[i] * chain_cost, 0.25 / world) for i in range(world)]
+    tot = sum(share)
+    cum = [0]
+    for x in share:
+        cum.append(cum[-1] + x / tot)
+    edges = [round(c * SHARD_DEN) for c in cum]
+    edges[0], edges[-1] = 0, SHARD_DEN
+    return edges[rank], edges[rank + 1], SHARD_DEN
+
+
+def range_of(total: int, bounds):
+    """[lo, lo + cnt) of `total` positions for (lo_num, hi_num, den) -- same arithmetic as csrc/prove.cu shard_range."""
+    lo_num, hi_num, den = bounds
+    lo, hi = total * lo_num // den, total * hi_num // den
+    return lo, hi - lo
+
+
 def exchange_chains(abc, dist):
     """Broadcast chain k of `abc` (a (3, n, 8) int32 tensor: the coset evaluations of a, b, c) from its owner rank, so that
     every rank ends up with all three.  NCCL over NVLink for CUDA tensors, gloo for CPU tensors."""

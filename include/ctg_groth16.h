@@ -196,6 +196,11 @@ int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_ins
  * GPU; host_pk is the full key on every rank).  A sharded key works with ctg_prove_partial only. */
 int32_t ctg_pk_upload_shard(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
                             int shard_index, int shard_count, ctg_pk** out);
+/* Weighted shards: keep positions [total * lo_num / den, total * hi_num / den) of every query.  The ranks' (lo_num, hi_num) must
+ * tile [0, den); ranks that also compute NTT chains of the witness map can be given fewer points (ctg/sharding.py: shard_bounds).
+ * ctg_pk_upload_shard(index, count) is the special case (index, index + 1, count). */
+int32_t ctg_pk_upload_range(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
+                            uint64_t lo_num, uint64_t hi_num, uint64_t den, ctg_pk** out);
 void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk);
 int32_t ctg_r1cs_upload(ctg_ctx* ctx, uint64_t num_instance, uint64_t num_witness, uint64_t num_constraints, const ctg_csr* a,
                         const ctg_csr* b, const ctg_csr* c, ctg_r1cs** out);

@@ -675,3 +675,34 @@ def test_setup_prove_tiny_domains(ctx, shape):
     proof = util.proof_to_py(ctx.prove(dpk, dr, ark.fr_mont_from_ints(z), fm(r), fm(s)))
     assert proof == G.create_proof(cs, want_pk, z, r, s)
     dpk.free(); dr.free(); dp.free()
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_prove_weighted_shards_combine(ctx, world):
+    """ctg_pk_upload_range with the weighted bounds the multi-GPU path uses (NTT-chain owners keep fewer points): the shards'
+    partial sums combine to the whole-key proof; malformed ranges are refused."""
+    from ctg import sharding
+    r1cs, zm, _ = S.mul_chain(10)
+    td_words, _ = S.trapdoor(seed=77)
+    dp = ctx.generate_parameters(r1cs, td_words)
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = fm(rnd.randrange(B.R_MOD)), fm(rnd.randrange(B.R_MOD))
+    whole = dp.to_device_pk(shard=(0, 1, 1))          # the full range is a whole key: ctg_prove accepts it
+    want = ctx.prove(whole, dr, zm, r, s)
+    whole.free()
+    parts = []
+    for rank in range(world):
+        b = sharding.shard_bounds(rank, world)
+        sh = dp.to_device_pk(shard=b)
+        parts.append(ctx.prove_partial(sh, dr, zm, r, s))
+        if rank == 0:
+            with pytest.raises(ctg.CtgError):
+                ctx.prove(sh, dr, zm, r, s)            # a partial key cannot produce a whole proof
+        sh.free()
+    got = ctx.prove_combine(np.stack(parts), r, s)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    for bad in ((3, 2, 8), (0, 9, 8), (0, 1, 0)):
+        with pytest.raises(ctg.CtgError):
+            dp.to_device_pk(shard=bad)
+    dr.free(); dp.free()

@@ -151,6 +151,27 @@ def test_shard_ranges_cover_everything():
         sh.shard_range(10, 2, 2)
 
 
+def test_weighted_shard_bounds_tile_everything():
+    import ctg.sharding as sh
+    for world in (1, 2, 3, 4, 8):
+        for dist_ntt in (False, True):
+            b = [sh.shard_bounds(r, world, dist_ntt) for r in range(world)]
+            assert b[0][0] == 0 and b[-1][1] == sh.SHARD_DEN and all(b[i][1] == b[i + 1][0] for i in range(world - 1))
+            for total in (0, 1, 7, 1 << 22, (1 << 24) + 3):
+                pos = 0
+                for r in range(world):
+                    lo, cnt = sh.range_of(total, b[r])
+                    assert lo == pos
+                    pos += cnt
+                assert pos == total
+    # owners of NTT chains keep fewer points; the equal split is reproduced when the witness map is replicated
+    b8 = [sh.shard_bounds(r, 8) for r in range(8)]
+    sizes = [hi - lo for lo, hi, _ in b8]
+    assert sizes[0] == sizes[1] == sizes[2] < sizes[3] and abs(sizes[3] - sizes[7]) <= 1
+    assert sh.shard_bounds(1, 4, distribute_ntt=False) == (sh.SHARD_DEN // 4, sh.SHARD_DEN // 2, sh.SHARD_DEN)
+    assert sh.range_of(1000, sh.shard_bounds(1, 4, False)) == sh.shard_range(1000, 1, 4)
+
+
 def test_chain_owners():
     import ctg.sharding as sh
     assert sh.chain_owners(1) == [0, 0, 0] and sh.chain_owners(2) == [0, 1, 0] and sh.chain_owners(8) == [0, 1, 2]
