@@ -71,6 +71,10 @@ struct ProveLane {
   MsmWorkspace ws[5];
   void* scratch = nullptr; size_t scratch_bytes = 0;
   cudaEvent_t ev_z = nullptr, ev_done[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  // the witness map and the H MSM are the critical path of a proof (the other four MSMs only need z): they run on a
+  // high-priority stream so that their blocks are scheduled ahead of the queued MSM blocks
+  cudaStream_t st_hi = nullptr;
+  cudaEvent_t ev_zfull = nullptr, ev_wm = nullptr;
   cudaEvent_t ev_t[16];   // stage timers
 };
 static constexpr int kMaxLanes = 4;

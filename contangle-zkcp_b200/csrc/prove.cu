@@ -326,7 +326,14 @@ static int32_t lane_init(ctg_ctx* ctx, int idx) {
     if (idx == 0 && i == 0) { L.st[0] = ctx->stream; continue; }
     CTG_CUDA(ctx, cudaStreamCreateWithFlags(&L.st[i], cudaStreamNonBlocking));
   }
+  {
+    int lo_pri = 0, hi_pri = 0;
+    CTG_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+    CTG_CUDA(ctx, cudaStreamCreateWithPriority(&L.st_hi, cudaStreamNonBlocking, hi_pri));
+  }
   CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_z, cudaEventDisableTiming));
+  CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_zfull, cudaEventDisableTiming));
+  CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_wm, cudaEventDisableTiming));
   for (auto& e : L.ev_done) CTG_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (auto& e : L.ev_t) CTG_CUDA(ctx, cudaEventCreate(&e));
   L.ready = true;
@@ -342,6 +349,8 @@ void lanes_destroy(ctg_ctx* ctx) {
       msm_ws_free(L.ws[i]);
     }
     if (L.scratch) cudaFree(L.scratch);
+    if (L.st_hi) { cudaStreamSynchronize(L.st_hi); cudaStreamDestroy(L.st_hi); }
+    cudaEventDestroy(L.ev_zfull); cudaEventDestroy(L.ev_wm);
     cudaEventDestroy(L.ev_z);
     for (auto& e : L.ev_done) cudaEventDestroy(e);
     for (auto& e : L.ev_t) cudaEventDestroy(e);
@@ -354,6 +363,7 @@ static int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
   if (bytes <= L.scratch_bytes) return CTG_OK;
   if (L.scratch) {
     for (int i = 0; i < 5; i++) CTG_CUDA(ctx, cudaStreamSynchronize(L.st[i]));
+    CTG_CUDA(ctx, cudaStreamSynchronize(L.st_hi));
     cudaFree(L.scratch);
     L.scratch = nullptr; L.scratch_bytes = 0;
   }
@@ -386,6 +396,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   G2XYZZ* d_g2 = (G2XYZZ*)(d_g1 + 4);
   ctg_proof* d_proof = (ctg_proof*)(d_g2 + 1);
   cudaStream_t s0 = L.st[0];
+  cudaStream_t sw = L.st_hi;   // witness map + H MSM
   int ne = 0;
   auto mark = [&](cudaStream_t st) { if (timed && ne < 16) cudaEventRecord(L.ev_t[ne], st); ne++; };
   if (phase != 2) {
@@ -407,6 +418,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
     if (s_lo > 0) CTG_CUDA(ctx, cudaMemcpyAsync(d_z, zh, s_lo * sizeof(Fr), cudaMemcpyHostToDevice, s0));
     if (s_hi < m) CTG_CUDA(ctx, cudaMemcpyAsync(d_z + s_hi, zh + s_hi, (m - s_hi) * sizeof(Fr), cudaMemcpyHostToDevice, s0));
   }
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_zfull, s0));
   mark(s0);                                                                   // 1
   // assignment-only MSMs on their own streams
   struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
@@ -426,19 +438,28 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   // witness map on the lane's main stream: the coset evaluations of a, b, c (the chains this rank owns) ...
   NttDomain* dom;
   CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
+  CTG_CUDA(ctx, cudaStreamWaitEvent(sw, L.ev_zfull, 0));
   for (int k = 0; k < 3; k++)
-    if (chain_mask & (1u << k)) CTG_TRY(witness_chain_dev(ctx, r, d_z, d_abc + (uint64_t)k * n, k, s0));
-  if (phase == 1) return CTG_OK;
+    if (chain_mask & (1u << k)) CTG_TRY(witness_chain_dev(ctx, r, d_z, d_abc + (uint64_t)k * n, k, sw));
+  if (phase == 1) {   // the caller synchronises s0 and then exchanges the chains
+    CTG_CUDA(ctx, cudaEventRecord(L.ev_wm, sw));
+    CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_wm, 0));
+    return CTG_OK;
+  }
   } else {
     ne = 10;
+    CTG_CUDA(ctx, cudaEventRecord(L.ev_zfull, s0));    // the exchanged chains were written on (or synchronised with) s0
+    CTG_CUDA(ctx, cudaStreamWaitEvent(sw, L.ev_zfull, 0));
   }
   // ... then (a b - c)/Z, the coset_ifft and the H MSM
-  CTG_TRY(witness_finish_dev(ctx, r, d_abc, s0));
-  set_h_tail_kernel<<<1, 32, 0, s0>>>(d_abc, n, r_m, s_m);
+  CTG_TRY(witness_finish_dev(ctx, r, d_abc, sw));
+  set_h_tail_kernel<<<1, 32, 0, sw>>>(d_abc, n, r_m, s_m);
   CTG_KERNEL_CHECK(ctx);
-  mark(s0);                                                                   // 10
-  CTG_TRY(msm_g1_run(ctx, L.ws[0], pk->h_ext, (const uint32_t*)(d_abc + pk->h_lo), pk->h_cnt, true, d_g1 + 3, s0, nullptr));
-  mark(s0);                                                                   // 11
+  mark(sw);                                                                   // 10
+  CTG_TRY(msm_g1_run(ctx, L.ws[0], pk->h_ext, (const uint32_t*)(d_abc + pk->h_lo), pk->h_cnt, true, d_g1 + 3, sw, nullptr));
+  mark(sw);                                                                   // 11
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_wm, sw));
+  CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_wm, 0));
   for (int i = 1; i < 5; i++) CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_done[i], 0));
   if (host_partials_out) {
     CTG_CUDA(ctx, cudaMemcpyAsync(host_partials_out, d_g1, 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ), cudaMemcpyDeviceToHost, s0));

@@ -94,24 +94,33 @@ def exchange_chains(abc, dist):
     return abc
 
 
-def sharded_prove(ctx, pk_shard, r1cs, z, r, s, dist, device=None, distribute_ntt=None):
+def sharded_prove(ctx, pk_shard, r1cs, z, r, s, dist, device=None, distribute_ntt=None, phases=None):
     """ark_groth16::create_proof over `world` GPUs.  Every rank calls this with its own context and key shard and the
     same (z, r, s); rank 0 returns (A, B, C), the other ranks return None.
     distribute_ntt (default: on for NCCL with more than one rank): the three NTT chains of the witness map are computed by
-    their owner ranks and broadcast over NVLink (n * 32 bytes each) instead of being replicated on every rank."""
+    their owner ranks and broadcast over NVLink (n * 32 bytes each) instead of being replicated on every rank.
+    phases: optional dict that receives this rank's wall-clock milliseconds per phase (diagnostics)."""
+    import time
     world = dist.get_world_size()
     if distribute_ntt is None:
         distribute_ntt = device is not None and world > 1
+    t0 = time.perf_counter()
     if distribute_ntt:
         import torch
         abc = torch.empty((3, r1cs.n, 8), dtype=torch.int32, device=device)
         ctx.prove_partial_begin(pk_shard, r1cs, z, r, s, chain_mask(dist.get_rank(), world), abc.data_ptr())
+        t1 = time.perf_counter()
         exchange_chains(abc, dist)
         torch.cuda.current_stream(device).synchronize()
+        t2 = time.perf_counter()
         part = ctx.prove_partial_finish(pk_shard, r1cs, r, s, abc.data_ptr())
     else:
         part = ctx.prove_partial(pk_shard, r1cs, z, r, s)
+        t1 = t2 = time.perf_counter()
+    t3 = time.perf_counter()
     allp = all_gather_partials(part, dist, device)
-    if dist.get_rank() == 0:
-        return ctx.prove_combine(allp, r, s)
-    return None
+    out = ctx.prove_combine(allp, r, s) if dist.get_rank() == 0 else None
+    if phases is not None:
+        t4 = time.perf_counter()
+        phases.update(begin_ms=(t1 - t0) * 1e3, exchange_ms=(t2 - t1) * 1e3, finish_ms=(t3 - t2) * 1e3, gather_combine_ms=(t4 - t3) * 1e3)
+    return out

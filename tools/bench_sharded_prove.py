@@ -15,6 +15,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--log-n", type=int, nargs="+", default=[20])
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--replicate-ntt", action="store_true", help="every rank runs the whole witness map (no chain exchange)")
+ap.add_argument("--chain-cost", type=float, default=None, help="weight of one NTT chain for the weighted shards (default: sharding.CHAIN_COST; 0 = equal shards)")
+ap.add_argument("--phases", action="store_true", help="print every rank's wall-clock phase times of the last repetition")
 ap.add_argument("--check", action="store_true", help="compare with the one-GPU proof of rank 0 (needs the full key on rank 0)")
 args = ap.parse_args()
 world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
@@ -32,7 +34,7 @@ for lg in args.log_n:
     t0 = time.perf_counter()
     dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])   # every rank generates the same key on its GPU, keeps only its shard
     setup_ms = (time.perf_counter() - t0) * 1e3
-    dpk = dp.to_device_pk(shard=sharding.shard_bounds(rank, world, dist_ntt))   # owners of NTT chains keep fewer points
+    dpk = dp.to_device_pk(shard=sharding.shard_bounds(rank, world, dist_ntt, sharding.CHAIN_COST if args.chain_cost is None else args.chain_cost))   # owners of NTT chains keep fewer points
     dr = ctx.upload_r1cs(r1cs)
     r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
     want = None
@@ -48,11 +50,17 @@ for lg in args.log_n:
     for _ in range(args.reps):
         dist.barrier(); torch.cuda.synchronize()
         t0 = time.perf_counter()
-        got = sharding.sharded_prove(ctx, dpk, dr, zm, r, s, dist, dev if world > 1 else None, distribute_ntt=dist_ntt)
+        ph = {}
+        got = sharding.sharded_prove(ctx, dpk, dr, zm, r, s, dist, dev if world > 1 else None, distribute_ntt=dist_ntt, phases=ph)
         torch.cuda.synchronize()
         t = torch.tensor([time.perf_counter() - t0], device=dev if world > 1 else "cpu")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         times.append(float(t[0]) * 1e3)
+    if args.phases:
+        allph = [None] * world
+        dist.all_gather_object(allph, {k: round(v, 2) for k, v in ph.items()})
+        if rank == 0:
+            print(json.dumps({"circuit": f"MulChain 2^{lg}", "phases_ms_by_rank": allph}), flush=True)
     if rank == 0:
         times.sort()
         line = {"bench": "groth16_prove_sharded", "circuit": f"MulChain 2^{lg}", "n_gpus": world, "ms_median": times[len(times) // 2], "ms_min": times[0],
