@@ -55,8 +55,10 @@ def chain_mask(rank: int, world: int) -> int:
 
 
 SHARD_DEN = 1 << 20
-CHAIN_COST = 0.033   # one NTT chain (SpMV + 2 transforms + the full assignment upload) relative to ALL five MSMs of a proof
-                     # (measured on B200: about 20 ms against 626 ms at 2^24, 5 ms against 147 ms at 2^22)
+CHAIN_COST = 0.0     # weight of one NTT chain relative to ALL five MSMs of a proof when sizing the shards.  A model of the
+                     # measured chain cost (0.033: about 20 ms against 626 ms at 2^24) was tried on 8 x B200 and lost to
+                     # equal shards (2^22: 37.1 vs 35.6 ms, 2^24: 108.9 vs 106.8 ms): the proof's critical path is the arrival
+                     # of the chains plus the final transform and H MSM on EVERY rank, not the owners' total work.
 
 
 def shard_bounds(rank: int, world: int, distribute_ntt: bool = True, chain_cost: float = CHAIN_COST):
@@ -65,7 +67,7 @@ def shard_bounds(rank: int, world: int, distribute_ntt: bool = True, chain_cost:
     same on every rank:  share_i = (1 + 3 c) / N - k_i c  with k_i chains on rank i.  The bounds of all ranks tile [0, den)."""
     if world < 1 or not 0 <= rank < world:
         raise ValueError("bad rank / world size")
-    if not distribute_ntt or world == 1:
+    if not distribute_ntt or world == 1 or chain_cost <= 0:
         return rank * SHARD_DEN // world, (rank + 1) * SHARD_DEN // world, SHARD_DEN
     owners = chain_owners(world)
     k = [owners.count(i) for i in range(world)]

@@ -692,7 +692,7 @@ def test_prove_weighted_shards_combine(ctx, world):
     whole.free()
     parts = []
     for rank in range(world):
-        b = sharding.shard_bounds(rank, world)
+        b = sharding.shard_bounds(rank, world, True, 0.033)
         sh = dp.to_device_pk(shard=b)
         parts.append(ctx.prove_partial(sh, dr, zm, r, s))
         if rank == 0:

@@ -155,7 +155,7 @@ def test_weighted_shard_bounds_tile_everything():
     import ctg.sharding as sh
     for world in (1, 2, 3, 4, 8):
         for dist_ntt in (False, True):
-            b = [sh.shard_bounds(r, world, dist_ntt) for r in range(world)]
+            b = [sh.shard_bounds(r, world, dist_ntt, 0.033 if dist_ntt else 0.0) for r in range(world)]
             assert b[0][0] == 0 and b[-1][1] == sh.SHARD_DEN and all(b[i][1] == b[i + 1][0] for i in range(world - 1))
             for total in (0, 1, 7, 1 << 22, (1 << 24) + 3):
                 pos = 0
@@ -165,11 +165,12 @@ def test_weighted_shard_bounds_tile_everything():
                     pos += cnt
                 assert pos == total
     # owners of NTT chains keep fewer points; the equal split is reproduced when the witness map is replicated
-    b8 = [sh.shard_bounds(r, 8) for r in range(8)]
+    b8 = [sh.shard_bounds(r, 8, True, 0.033) for r in range(8)]
     sizes = [hi - lo for lo, hi, _ in b8]
     assert sizes[0] == sizes[1] == sizes[2] < sizes[3] and abs(sizes[3] - sizes[7]) <= 1
     assert sh.shard_bounds(1, 4, distribute_ntt=False) == (sh.SHARD_DEN // 4, sh.SHARD_DEN // 2, sh.SHARD_DEN)
     assert sh.range_of(1000, sh.shard_bounds(1, 4, False)) == sh.shard_range(1000, 1, 4)
+    assert sh.shard_bounds(2, 8) == (2 * sh.SHARD_DEN // 8, 3 * sh.SHARD_DEN // 8, sh.SHARD_DEN)   # default: equal shards
 
 
 def test_chain_owners():
