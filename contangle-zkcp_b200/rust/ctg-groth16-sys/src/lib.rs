@@ -49,6 +49,8 @@ pub struct ctg_params_out {
     pub b_g2_query: *mut ctg_g2_affine, pub h_query: *mut ctg_g1_affine, pub l_query: *mut ctg_g1_affine,
 }
 #[repr(C)] #[derive(Clone, Copy)] pub struct ctg_proof_partial { pub a: ctg_g1_xyzz, pub b1: ctg_g1_xyzz, pub l: ctg_g1_xyzz, pub h: ctg_g1_xyzz, pub b2: ctg_g2_xyzz }
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct ctg_msm_plan { pub window_bits: i32, pub windows: i32, pub copies: i32, pub bucket_sets: i32, pub buckets_per_set: u32 }
 #[repr(C)] pub struct ctg_csr { pub row_ptr: *const u64, pub col: *const u32, pub val: *const ctg_fr }
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct ctg_timings {
@@ -105,4 +107,31 @@ extern "C" {
     pub fn ctg_proof_deserialize(in192: *const u8, check_subgroup: c_int, out: *mut ctg_proof) -> i32;
     pub fn ctg_host_alloc(ctx: *mut ctg_ctx, bytes: usize, h_out: *mut *mut c_void) -> i32;
     pub fn ctg_host_free(ctx: *mut ctg_ctx, h_ptr: *mut c_void) -> i32;
+    pub fn ctg_pk_upload_range(ctx: *mut ctg_ctx, pk: *const ctg_pk_view, num_instance: u64, num_constraints: u64, copies: c_int, c_bits: c_int,
+                               lo_num: u64, hi_num: u64, den: u64, out: *mut *mut ctg_pk) -> i32;
+    // primitives, device-pointer variants, tuning knobs and harness helpers (tests / benches / ncu captures)
+    pub fn ctg_ctx_set_ba_levels(ctx: *mut ctg_ctx, levels: c_int) -> i32;
+    pub fn ctg_ctx_set_msm_split(ctx: *mut ctg_ctx, parts: c_int) -> i32;
+    pub fn ctg_dev_alloc(ctx: *mut ctg_ctx, bytes: usize, d_out: *mut *mut c_void) -> i32;
+    pub fn ctg_dev_free(ctx: *mut ctg_ctx, d_ptr: *mut c_void) -> i32;
+    pub fn ctg_h2d(ctx: *mut ctg_ctx, d_dst: *mut c_void, h_src: *const c_void, bytes: usize) -> i32;
+    pub fn ctg_d2h(ctx: *mut ctg_ctx, h_dst: *mut c_void, d_src: *const c_void, bytes: usize) -> i32;
+    pub fn ctg_field_op_batch(ctx: *mut ctg_ctx, field: c_int, op: c_int, a: *const c_void, b: *const c_void, out: *mut c_void, n: usize) -> i32;
+    pub fn ctg_fr_mul_batch(ctx: *mut ctg_ctx, a: *const ctg_fr, b: *const ctg_fr, out: *mut ctg_fr, n: usize) -> i32;
+    pub fn ctg_fq_mul_batch(ctx: *mut ctg_ctx, a: *const ctg_fq, b: *const ctg_fq, out: *mut ctg_fq, n: usize) -> i32;
+    pub fn ctg_imad_peak_probe(ctx: *mut ctg_ctx, imad_per_s: *mut f64, fq_mul_per_s: *mut f64) -> i32;
+    pub fn ctg_ntt_fr_dev(ctx: *mut ctg_ctx, d_data: *mut c_void, log_n: u32, inverse: c_int, coset: c_int) -> i32;
+    pub fn ctg_bases_progression_g1(ctx: *mut ctg_ctx, g: *const ctg_g1_affine, a: *const ctg_fr, b: *const ctg_fr, n: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_bases) -> i32;
+    pub fn ctg_bases_progression_g2(ctx: *mut ctg_ctx, g: *const ctg_g2_affine, a: *const ctg_fr, b: *const ctg_fr, n: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_bases) -> i32;
+    pub fn ctg_bases_download(ctx: *mut ctg_ctx, bases: *const ctg_bases, first: u64, count: u64, host_points: *mut c_void) -> i32;
+    pub fn ctg_bases_len(bases: *const ctg_bases) -> u64;
+    pub fn ctg_bases_plan(bases: *const ctg_bases, out: *mut ctg_msm_plan) -> i32;
+    pub fn ctg_msm_g1_dev(ctx: *mut ctg_ctx, bases: *const ctg_bases, d_scalars: *const c_void, n: u64, flags: u32, d_out_xyzz: *mut c_void) -> i32;
+    pub fn ctg_msm_g2_dev(ctx: *mut ctg_ctx, bases: *const ctg_bases, d_scalars: *const c_void, n: u64, flags: u32, d_out_xyzz: *mut c_void) -> i32;
+    pub fn ctg_msm_g1_partial(ctx: *mut ctg_ctx, bases: *const ctg_bases, scalars: *const ctg_fr, n: u64, flags: u32, out: *mut ctg_g1_xyzz) -> i32;
+    pub fn ctg_msm_g2_partial(ctx: *mut ctg_ctx, bases: *const ctg_bases, scalars: *const ctg_fr, n: u64, flags: u32, out: *mut ctg_g2_xyzz) -> i32;
+    pub fn ctg_g1_combine(ctx: *mut ctg_ctx, partials: *const ctg_g1_xyzz, k: u32, out: *mut ctg_g1_affine) -> i32;
+    pub fn ctg_g2_combine(ctx: *mut ctg_ctx, partials: *const ctg_g2_xyzz, k: u32, out: *mut ctg_g2_affine) -> i32;
+    pub fn ctg_g1_combine_dev(ctx: *mut ctg_ctx, d_partials: *const c_void, k: u32, d_out_affine: *mut c_void) -> i32;
+    pub fn ctg_g2_combine_dev(ctx: *mut ctg_ctx, d_partials: *const c_void, k: u32, d_out_affine: *mut c_void) -> i32;
 }

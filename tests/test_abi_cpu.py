@@ -54,3 +54,11 @@ def test_product_does_not_reference_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", "Makefile", ".rs", ".toml")):
                 txt = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in txt, os.path.join(dirpath, f)
+
+
+def test_rust_sys_crate_binds_every_declared_symbol():
+    """The Rust -sys crate is source only (no rustc here); at least keep its extern block in step with the header."""
+    rs = open(os.path.join(ROOT, "contangle-zkcp_b200", "rust", "ctg-groth16-sys", "src", "lib.rs")).read()
+    bound = set(re.findall(r"pub fn (ctg_[a-z0-9_]+)", rs))
+    missing = [s for s in _declared_symbols() if s not in bound]
+    assert not missing, missing
