@@ -384,6 +384,25 @@ def extras(ctx, torch, dev, stream, S, args):
     out["ntt_fr_forward"] = ntt
     out["ntt_note"] = ("radix-2 NTT over a 255-bit field is integer-bound on B200: 68*log2(n) MAC32 per element against 64 B of "
                        "compulsory traffic; frac_of_mac32_peak is the binding roofline, frac_of_hbm_peak the one the north star names")
+    # bulk Poseidon Merkle tree of a ciphertext: the reference's rounds / alpha, seeded constants
+    import random as _random
+    prnd = _random.Random(11)
+    full_r, part_r, alpha = 8, 31, 17
+    pos = ctx.poseidon(full_r, part_r, alpha, S.fr_mont([prnd.randrange(S.R_MOD) for _ in range(9)]).reshape(3, 3, 8),
+                       S.fr_mont([prnd.randrange(S.R_MOD) for _ in range(3 * (full_r + part_r))]).reshape(full_r + part_r, 3, 8))
+    fr_products = 9 * (full_r + part_r) + 5 * (3 * full_r + part_r)
+    trees = {}
+    for lg in (16, 20, 22):
+        n = 1 << lg
+        leaves = torch.randint(0, 1 << 28, (n, 8), device=dev, dtype=torch.int32)
+        dig, inner = torch.empty_like(leaves), torch.empty_like(leaves)
+        ms = ev_time(lambda: pos.merkle_tree_dev(leaves.data_ptr(), n, dig.data_ptr(), inner.data_ptr()), 3)
+        trees[f"2^{lg}"] = {"ms": ms, "Mpermutations_per_s": (2 * n - 1) / ms / 1e3,
+                            "frac_of_mac32_peak": (2 * n - 1) * fr_products * 136.0 / (ms * 1e-3) / mac_peak}
+        del leaves, dig, inner
+    pos.free()
+    out["poseidon_merkle_tree"] = {"params": {"full_rounds": full_r, "partial_rounds": part_r, "alpha": alpha, "fr_products_per_permutation": fr_products},
+                                   "leaves": trees}
     msm = {}
     for lg in (16, 18, 20, 24):
         n = 1 << lg

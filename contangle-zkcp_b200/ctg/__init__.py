@@ -38,6 +38,8 @@ EXPORTS = [
     "ctg_params_deserialize_unchecked", "ctg_params_serialize_unchecked", "ctg_params_serialize_vk",
     "ctg_proof_serialize", "ctg_proof_deserialize", "ctg_prove_partial_begin", "ctg_prove_partial_finish",
     "ctg_pk_upload_range",
+    "ctg_poseidon_new", "ctg_poseidon_free", "ctg_poseidon_hash_batch", "ctg_poseidon_hash_batch_dev",
+    "ctg_poseidon_merkle_tree", "ctg_poseidon_merkle_tree_dev",
 ]
 
 
@@ -99,7 +101,7 @@ def load():
         lib.ctg_last_error.restype = C.c_char_p
         lib.ctg_launch_count.restype = C.c_uint64
         lib.ctg_bases_len.restype = C.c_uint64
-        for name in ("ctg_ctx_destroy", "ctg_bases_free", "ctg_pk_free", "ctg_r1cs_free", "ctg_params_free"):
+        for name in ("ctg_ctx_destroy", "ctg_bases_free", "ctg_pk_free", "ctg_r1cs_free", "ctg_params_free", "ctg_poseidon_free"):
             getattr(lib, name).restype = None
         _lib = lib
     return _lib
@@ -219,6 +221,19 @@ class Context:
 
     def ntt_dev(self, d_ptr, log_n, inverse=False, coset=False):
         self._check(load().ctg_ntt_fr_dev(self.h, C.c_void_p(d_ptr), C.c_uint32(log_n), int(inverse), int(coset)))
+
+    # ---- bulk Poseidon (witness-side crypto upstream of the prover)
+    def poseidon(self, full_rounds, partial_rounds, alpha, mds, ark):
+        """ark_sponge::poseidon::PoseidonParameters::new(full_rounds, partial_rounds, alpha, mds, ark) on the device;
+        mds (3, 3, 8) and ark (rounds, 3, 8): Montgomery Fr words."""
+        mds = np.ascontiguousarray(mds, dtype=np.uint32)
+        ark = np.ascontiguousarray(ark, dtype=np.uint32)
+        if mds.shape != (3, 3, FR_W) or ark.shape != (int(full_rounds) + int(partial_rounds), 3, FR_W):
+            raise CtgError("poseidon: mds must be (3, 3, 8) and ark (full + partial, 3, 8) Fr words")
+        h = C.c_void_p()
+        self._check(load().ctg_poseidon_new(self.h, C.c_uint32(full_rounds), C.c_uint32(partial_rounds), C.c_uint32(alpha),
+                                            _ptr(mds), _ptr(ark), C.byref(h)))
+        return Poseidon(self, h)
 
     # ---- bases / MSM
     def bases_g1(self, points, copies=0, c_bits=0):
@@ -469,6 +484,70 @@ class DeviceR1cs:
         if self.handle:
             load().ctg_r1cs_free(self.ctx.h, self.handle)
             self.handle = None
+
+
+class Poseidon:
+    """Device-resident PoseidonParameters (rate 2, capacity 1): bulk CRH / sponge hashes and the ciphertext Merkle tree
+    (circuits-ark/src/sample_entries.rs:127-134, encryption.rs:154-172)."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self.handle = ctx, handle
+
+    def free(self):
+        if self.handle:
+            load().ctg_poseidon_free(self.ctx.h, self.handle)
+            self.handle = None
+
+    def hash_batch(self, inputs):
+        """inputs (n, k, 8) -> (n, 8): first squeezed element of a fresh sponge that absorbed the k elements of each row
+        (k = 1: leaf CRH, k = 2: TwoToOneCRH / the ElGamal pad of an affine point)."""
+        inputs = np.ascontiguousarray(inputs, dtype=np.uint32)
+        if inputs.ndim != 3 or inputs.shape[2] != FR_W:
+            raise CtgError("poseidon: inputs must be (n, k, 8) Fr words")
+        n, k = inputs.shape[0], inputs.shape[1]
+        out = np.empty((n, FR_W), dtype=np.uint32)
+        self.ctx._check(load().ctg_poseidon_hash_batch(self.ctx.h, self.handle, _ptr(inputs), C.c_uint64(n), C.c_uint32(k), _ptr(out)))
+        return out
+
+    def hash_batch_dev(self, d_in, n, k, d_out):
+        self.ctx._check(load().ctg_poseidon_hash_batch_dev(self.ctx.h, self.handle, C.c_void_p(d_in), C.c_uint64(n), C.c_uint32(k), C.c_void_p(d_out)))
+
+    def merkle_tree(self, leaves):
+        """MerkleTree::new(params, params, leaves) with one field element per leaf -> MerkleTree (leaf_nodes, non_leaf_nodes)."""
+        leaves = _arr(leaves, FR_W)
+        n = leaves.shape[0]
+        digests = np.empty((n, FR_W), dtype=np.uint32)
+        inner = np.empty((max(n - 1, 0), FR_W), dtype=np.uint32)
+        self.ctx._check(load().ctg_poseidon_merkle_tree(self.ctx.h, self.handle, _ptr(leaves), C.c_uint64(n), _ptr(digests), _ptr(inner)))
+        return MerkleTree(digests, inner)
+
+    def merkle_tree_dev(self, d_leaves, n, d_leaf_digests, d_inner):
+        self.ctx._check(load().ctg_poseidon_merkle_tree_dev(self.ctx.h, self.handle, C.c_void_p(d_leaves), C.c_uint64(n),
+                                                            C.c_void_p(d_leaf_digests), C.c_void_p(d_inner)))
+
+
+class MerkleTree:
+    """Nodes of ark_crypto_primitives::merkle_tree::MerkleTree in its own order: leaf_nodes (n, 8) and non_leaf_nodes
+    (n - 1, 8) in heap order, root first."""
+
+    def __init__(self, leaf_nodes, non_leaf_nodes):
+        self.leaf_nodes, self.non_leaf_nodes = leaf_nodes, non_leaf_nodes
+
+    def root(self):
+        return self.non_leaf_nodes[0]
+
+    def generate_proof(self, index):
+        """MerkleTree::generate_proof: (leaf_sibling_hash, auth_path root side first, leaf_index)."""
+        n = self.leaf_nodes.shape[0]
+        if not 0 <= index < n:
+            raise CtgError("merkle tree: leaf index out of range")
+        sibling = self.leaf_nodes[index ^ 1]
+        node = (n - 1 + index - 1) // 2
+        path = []
+        while node != 0:
+            path.append(self.non_leaf_nodes[node + 1 if node % 2 == 1 else node - 1])
+            node = (node - 1) // 2
+        return sibling, path[::-1], index
 
 
 class DeviceParams:

@@ -219,4 +219,43 @@ inline Proof proof_from_bytes(const std::vector<uint8_t>& bytes, bool check_subg
   return Proof{raw.a, raw.b, raw.c};
 }
 
+// ---- bulk Poseidon / ciphertext Merkle tree (circuits-ark/src/sample_entries.rs:127-134, encryption.rs:154-172) ----
+// ark_sponge::poseidon::PoseidonParameters (rate 2, capacity 1) resident on the device.
+struct MerkleTree {               // ark_crypto_primitives::merkle_tree::MerkleTree node arrays, in its order
+  std::vector<ctg_fr> leaf_nodes;      // CRH([leaf])
+  std::vector<ctg_fr> non_leaf_nodes;  // heap order, root first
+  const ctg_fr& root() const { return non_leaf_nodes[0]; }
+};
+class Poseidon {
+ public:
+  // mds: 9 elements row-major; ark: (full_rounds + partial_rounds) * 3 elements; Montgomery images
+  Poseidon(const Context& ctx, uint32_t full_rounds, uint32_t partial_rounds, uint32_t alpha, const std::vector<ctg_fr>& mds, const std::vector<ctg_fr>& ark)
+      : ctx_(ctx) {
+    if (mds.size() != 9 || ark.size() != (size_t)3 * (full_rounds + partial_rounds)) throw Error(CTG_ERR_INVALID, "poseidon: parameter shape");
+    ctx_.check(ctg_poseidon_new(ctx_.raw(), full_rounds, partial_rounds, alpha, mds.data(), ark.data(), &p_));
+  }
+  ~Poseidon() { ctg_poseidon_free(ctx_.raw(), p_); }
+  Poseidon(const Poseidon&) = delete;
+  Poseidon& operator=(const Poseidon&) = delete;
+  // CRH::evaluate for n inputs of k elements each (k = 2: TwoToOneCRH::evaluate)
+  std::vector<ctg_fr> hash_batch(const std::vector<ctg_fr>& inputs, uint32_t k) const {
+    if (k == 0 || inputs.size() % k) throw Error(CTG_ERR_INVALID, "poseidon: inputs must be n * k elements");
+    std::vector<ctg_fr> out(inputs.size() / k);
+    ctx_.check(ctg_poseidon_hash_batch(ctx_.raw(), p_, inputs.data(), out.size(), k, out.data()));
+    return out;
+  }
+  // MerkleTree::new(params, params, leaves) with one field element per leaf
+  MerkleTree merkle_tree(const std::vector<ctg_fr>& leaves) const {
+    MerkleTree t;
+    t.leaf_nodes.resize(leaves.size());
+    t.non_leaf_nodes.resize(leaves.empty() ? 0 : leaves.size() - 1);
+    ctx_.check(ctg_poseidon_merkle_tree(ctx_.raw(), p_, leaves.data(), leaves.size(), t.leaf_nodes.data(), t.non_leaf_nodes.data()));
+    return t;
+  }
+
+ private:
+  const Context& ctx_;
+  ctg_poseidon* p_ = nullptr;
+};
+
 }  // namespace ctg

@@ -17,6 +17,7 @@ pub const CTG_MSM_TIMED: u32 = 0x100;
 #[repr(C)] pub struct ctg_pk { _p: [u8; 0] }
 #[repr(C)] pub struct ctg_r1cs { _p: [u8; 0] }
 #[repr(C)] pub struct ctg_params { _p: [u8; 0] }
+#[repr(C)] pub struct ctg_poseidon { _p: [u8; 0] }
 
 /// ark-ff Fp256 memory image: [u64; 4] little-endian Montgomery limbs == [u32; 8]
 #[repr(C)] #[derive(Clone, Copy, Default)] pub struct ctg_fr { pub v: [u32; 8] }
@@ -109,6 +110,16 @@ extern "C" {
     pub fn ctg_host_free(ctx: *mut ctg_ctx, h_ptr: *mut c_void) -> i32;
     pub fn ctg_pk_upload_range(ctx: *mut ctg_ctx, pk: *const ctg_pk_view, num_instance: u64, num_constraints: u64, copies: c_int, c_bits: c_int,
                                lo_num: u64, hi_num: u64, den: u64, out: *mut *mut ctg_pk) -> i32;
+    // bulk Poseidon / ciphertext Merkle tree (circuits-ark/src/sample_entries.rs:127-134, encryption.rs:154-172)
+    pub fn ctg_poseidon_new(ctx: *mut ctg_ctx, full_rounds: u32, partial_rounds: u32, alpha: u32, mds: *const ctg_fr, ark: *const ctg_fr,
+                            out: *mut *mut ctg_poseidon) -> i32;
+    pub fn ctg_poseidon_free(ctx: *mut ctg_ctx, p: *mut ctg_poseidon);
+    pub fn ctg_poseidon_hash_batch(ctx: *mut ctg_ctx, p: *const ctg_poseidon, input: *const ctg_fr, n: u64, k: u32, out: *mut ctg_fr) -> i32;
+    pub fn ctg_poseidon_hash_batch_dev(ctx: *mut ctg_ctx, p: *const ctg_poseidon, d_in: *const c_void, n: u64, k: u32, d_out: *mut c_void) -> i32;
+    pub fn ctg_poseidon_merkle_tree(ctx: *mut ctg_ctx, p: *const ctg_poseidon, leaves: *const ctg_fr, n: u64, leaf_digests: *mut ctg_fr,
+                                    inner: *mut ctg_fr) -> i32;
+    pub fn ctg_poseidon_merkle_tree_dev(ctx: *mut ctg_ctx, p: *const ctg_poseidon, d_leaves: *const c_void, n: u64, d_leaf_digests: *mut c_void,
+                                        d_inner: *mut c_void) -> i32;
     // primitives, device-pointer variants, tuning knobs and harness helpers (tests / benches / ncu captures)
     pub fn ctg_ctx_set_ba_levels(ctx: *mut ctg_ctx, levels: c_int) -> i32;
     pub fn ctg_ctx_set_msm_split(ctx: *mut ctg_ctx, parts: c_int) -> i32;

@@ -282,6 +282,31 @@ int32_t ctg_params_serialize_vk(ctg_ctx* ctx, const ctg_params* params, uint8_t*
 int32_t ctg_proof_serialize(const ctg_proof* proof, uint8_t* out192);
 int32_t ctg_proof_deserialize(const uint8_t* in192, int check_subgroup, ctg_proof* out);
 
+/* ---- bulk Poseidon over Fr: sponge hashes and the ciphertext Merkle tree ----------------------
+ * Replaces, for many items at once, the native (out-of-circuit) Poseidon work upstream of the prover:
+ *   circuits-ark/src/sample_entries.rs:127-134  build_merkle_tree = MerkleTree::new(params, params, leaves) with one field
+ *       element per leaf (leaf digest = poseidon::CRH([e]), inner digest = TwoToOneCRH(l, r) = CRH([l, r]));
+ *   circuits-ark/src/encryption.rs:154-172      PoseidonSponge::new(params).absorb(..).squeeze_field_elements(1).
+ * Sponge as ark-sponge ^0.3.0 PoseidonSponge: width 3 (rate 2, capacity 1, rate cells first), full_rounds/2 full rounds,
+ * partial_rounds partial rounds (S-box on cell 0), full_rounds/2 full rounds; every round adds ark[round][0..3), applies
+ * x^alpha and multiplies by mds (new[i] = sum_j mds[i][j] * state[j]).  Parameters are the caller's PoseidonParameters
+ * (circuits-ark/src/poseidon.rs:13-41): mds = 3 x 3 row-major, ark = (full + partial) x 3, Montgomery Fr images.
+ * Errors: CTG_ERR_INVALID for an odd or zero full_rounds, full + partial > 128, alpha < 2, k = 0, or a leaf count that is
+ * not a power of two >= 2 (arkworks' MerkleTree::new asserts the same). */
+typedef struct ctg_poseidon ctg_poseidon;
+int32_t ctg_poseidon_new(ctg_ctx* ctx, uint32_t full_rounds, uint32_t partial_rounds, uint32_t alpha, const ctg_fr* mds, const ctg_fr* ark,
+                         ctg_poseidon** out);
+void ctg_poseidon_free(ctg_ctx* ctx, ctg_poseidon* p);
+/* out[i] = the first squeezed element after absorbing in[i*k .. i*k + k) into a fresh sponge (k >= 1; k = 1 is the leaf CRH,
+ * k = 2 the two-to-one CRH, k = 2 with an affine point's (x, y) the ElGamal pad of encrypt()).  _dev: device pointers. */
+int32_t ctg_poseidon_hash_batch(ctg_ctx* ctx, const ctg_poseidon* p, const ctg_fr* in, uint64_t n, uint32_t k, ctg_fr* out);
+int32_t ctg_poseidon_hash_batch_dev(ctg_ctx* ctx, const ctg_poseidon* p, const void* d_in, uint64_t n, uint32_t k, void* d_out);
+/* Whole tree over n = 2^d leaves: leaf_digests[n] (may be NULL in the host variant) and inner[n - 1] in heap order -- root at 0,
+ * children of node i at 2i + 1 and 2i + 2, the last level's children being leaf digests 2j and 2j + 1 (the order of arkworks'
+ * MerkleTree::non_leaf_nodes / leaf_nodes, from which generate_proof reads its Path). */
+int32_t ctg_poseidon_merkle_tree(ctg_ctx* ctx, const ctg_poseidon* p, const ctg_fr* leaves, uint64_t n, ctg_fr* leaf_digests, ctg_fr* inner);
+int32_t ctg_poseidon_merkle_tree_dev(ctg_ctx* ctx, const ctg_poseidon* p, const void* d_leaves, uint64_t n, void* d_leaf_digests, void* d_inner);
+
 #ifdef __cplusplus
 }
 #endif

@@ -75,6 +75,24 @@ int main(int argc, char** argv) {
     ctg::ConstraintSystem other = cs;
     other.a.pop_back(); other.b.pop_back(); other.c.pop_back();
     try { ctg::create_proof(dpk, other, r, s); std::fprintf(stderr, "shape mismatch accepted\n"); return 1; } catch (const ctg::Error&) {}
+    // bulk Poseidon: the Merkle tree over 8 leaves equals the tree rebuilt with the bulk hashes (values themselves are
+    // checked against the big-int restatement in tests/test_poseidon.py); r, s and small constants serve as field elements
+    {
+      std::vector<ctg_fr> mds(9), ark(3 * 39), leaves(8);
+      for (size_t i = 0; i < mds.size(); i++) { mds[i] = r; mds[i].v[0] ^= (uint32_t)(i + 1); mds[i].v[7] &= 0x3fffffffu; }
+      for (size_t i = 0; i < ark.size(); i++) { ark[i] = s; ark[i].v[1] ^= (uint32_t)(i * 2654435761u); ark[i].v[7] &= 0x3fffffffu; }
+      for (size_t i = 0; i < leaves.size(); i++) { leaves[i] = r; leaves[i].v[2] ^= (uint32_t)(i + 7); leaves[i].v[7] &= 0x3fffffffu; }
+      ctg::Poseidon pos(ctx, 8, 31, 17, mds, ark);
+      ctg::MerkleTree tree = pos.merkle_tree(leaves);
+      std::vector<ctg_fr> level = pos.hash_batch(leaves, 1);
+      if (std::memcmp(level.data(), tree.leaf_nodes.data(), 8 * sizeof(ctg_fr)) != 0) { std::fprintf(stderr, "leaf digests differ\n"); return 1; }
+      for (size_t width = 4; width >= 1; width /= 2) {
+        level = pos.hash_batch(level, 2);
+        if (std::memcmp(level.data(), &tree.non_leaf_nodes[width - 1], width * sizeof(ctg_fr)) != 0) { std::fprintf(stderr, "tree level differs\n"); return 1; }
+      }
+      if (std::memcmp(&tree.root(), level.data(), sizeof(ctg_fr)) != 0) { std::fprintf(stderr, "root differs\n"); return 1; }
+      try { pos.merkle_tree(std::vector<ctg_fr>(leaves.begin(), leaves.begin() + 3)); std::fprintf(stderr, "3 leaves accepted\n"); return 1; } catch (const ctg::Error&) {}
+    }
     std::printf("ok %zu bytes of key, proof %zu bytes\n", slurp(out_dir + "/circuit.zkey").size(), bytes.size());
     return 0;
   } catch (const ctg::Error& e) {
