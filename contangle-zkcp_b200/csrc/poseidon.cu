@@ -11,7 +11,7 @@
 // squeeze after absorb = one permutation, output state[0].  Parameters are the caller's (the reference reads its own from
 // circuits-ark/src/parameters.rs: alpha 17, 8 full and 31 partial rounds); nothing here fixes them beyond the width.
 //
-// One thread owns one hash: 3 state cells in registers, round constants and the MDS matrix staged once per CTA in shared
+// Wide levels: one thread owns one hash, 3 state cells in registers, round constants and the MDS matrix staged once per CTA in shared
 // memory (a warp reads the same constant at the same time, i.e. a broadcast).  A permutation is
 // 9 * rounds + (sbox muls) * (3 * full + partial) Fr products -- 626 for the reference's parameters -- against 64..96 bytes of
 // HBM traffic per hash, so the kernels are bound by the integer pipe like the NTT butterflies, not by HBM.
@@ -119,8 +119,53 @@ __global__ void __launch_bounds__(kPosThreads) poseidon_compress_kernel(PosCfg c
   pos_store(parents + i, s[0]);
 }
 
+// Narrow tree levels are latency-bound (a permutation is one dependent chain of products), so below kSplitBelow nodes a hash
+// is spread over a group of four lanes, one state cell per lane (the fourth idles): the three S-boxes of a full round and the
+// three rows of the MDS product run side by side and the chain drops from 14..24 to 8 products per round.  The cells meet
+// through warp shuffles.  arity 1: digest of one element (leaf level); arity 2: TwoToOneCRH.
+static constexpr uint64_t kSplitBelow = 1ull << 15;
+
+__device__ __forceinline__ Fr pos_shfl(const Fr& v, unsigned src) {
+  Fr r;
+#pragma unroll
+  for (int w = 0; w < 8; w++) r.v[w] = __shfl_sync(0xffffffffu, v.v[w], src);
+  return r;
+}
+
+__global__ void __launch_bounds__(kPosThreads) poseidon_split_kernel(PosCfg c, const Fr* __restrict__ in, uint64_t n, uint32_t arity, Fr* __restrict__ out) {
+  extern __shared__ uint4 pos_smem[];
+  Fr* sc = reinterpret_cast<Fr*>(pos_smem);
+  pos_stage(sc, c);
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t i = t >> 2;
+  const uint32_t lane_cell = (uint32_t)(t & 3);
+  const uint32_t cell = lane_cell < 2 ? lane_cell : 2;     // the idle fourth lane shadows cell 2; nothing reads it
+  const bool active = i < n;                                // whole groups are active or not; every lane stays for the shuffles
+  Fr s = Fr::zero();
+  if (active && lane_cell < arity) s = pos_load(in + (uint64_t)arity * i + lane_cell);
+  const unsigned base = (threadIdx.x & 31u) & ~3u;
+  const uint32_t rounds = c.full_rounds + c.partial_rounds;
+  const uint32_t half = c.full_rounds / 2;
+  const Fr* row = sc + 3 * rounds + 3 * cell;
+  for (uint32_t r = 0; r < rounds; r++) {
+    const bool full = r < half || r >= half + c.partial_rounds;
+    Fr x = s + sc[3 * r + cell];
+    if (lane_cell == 0 || (full && lane_cell < 3)) x = pos_sbox(x, c.alpha);
+    const Fr t0 = pos_shfl(x, base), t1 = pos_shfl(x, base + 1), t2 = pos_shfl(x, base + 2);
+    s = row[0] * t0 + row[1] * t1 + row[2] * t2;
+  }
+  if (active && lane_cell == 0) pos_store(out + i, s);
+}
+
 static size_t pos_smem_bytes(const ctg_poseidon* p) { return (size_t)(3 * (p->full_rounds + p->partial_rounds) + 9) * sizeof(Fr); }
 static PosCfg pos_cfg(const ctg_poseidon* p) { return PosCfg{p->d_consts, p->full_rounds, p->partial_rounds, p->alpha}; }
+
+static int32_t pos_split_dev(ctg_ctx* ctx, const ctg_poseidon* p, const Fr* d_in, uint64_t n, uint32_t arity, Fr* d_out, cudaStream_t st) {
+  const uint64_t blocks = (4 * n + kPosThreads - 1) / kPosThreads;
+  poseidon_split_kernel<<<(unsigned)blocks, kPosThreads, pos_smem_bytes(p), st>>>(pos_cfg(p), d_in, n, arity, d_out);
+  CTG_KERNEL_CHECK(ctx);
+  return CTG_OK;
+}
 
 static int32_t pos_hash_dev(ctg_ctx* ctx, const ctg_poseidon* p, const Fr* d_in, uint64_t n, uint32_t k, Fr* d_out, cudaStream_t st) {
   if (n == 0) return CTG_OK;
@@ -132,13 +177,18 @@ static int32_t pos_hash_dev(ctg_ctx* ctx, const ctg_poseidon* p, const Fr* d_in,
 
 // d_leaf_digests: n entries; d_inner: n - 1 entries in heap order (root at 0, children of i at 2i+1 and 2i+2)
 static int32_t pos_merkle_dev(ctg_ctx* ctx, const ctg_poseidon* p, const Fr* d_leaves, uint64_t n, Fr* d_leaf_digests, Fr* d_inner, cudaStream_t st) {
-  CTG_TRY(pos_hash_dev(ctx, p, d_leaves, n, 1, d_leaf_digests, st));
+  if (n < kSplitBelow) CTG_TRY(pos_split_dev(ctx, p, d_leaves, n, 1, d_leaf_digests, st));
+  else CTG_TRY(pos_hash_dev(ctx, p, d_leaves, n, 1, d_leaf_digests, st));
   const Fr* children = d_leaf_digests;
   for (uint64_t np = n / 2; np >= 1; np /= 2) {
     Fr* parents = d_inner + (np - 1);       // level with np nodes starts at heap index np - 1
-    const uint64_t blocks = (np + kPosThreads - 1) / kPosThreads;
-    poseidon_compress_kernel<<<(unsigned)blocks, kPosThreads, pos_smem_bytes(p), st>>>(pos_cfg(p), children, np, parents);
-    CTG_KERNEL_CHECK(ctx);
+    if (np < kSplitBelow) {
+      CTG_TRY(pos_split_dev(ctx, p, children, np, 2, parents, st));
+    } else {
+      const uint64_t blocks = (np + kPosThreads - 1) / kPosThreads;
+      poseidon_compress_kernel<<<(unsigned)blocks, kPosThreads, pos_smem_bytes(p), st>>>(pos_cfg(p), children, np, parents);
+      CTG_KERNEL_CHECK(ctx);
+    }
     children = parents;
   }
   return CTG_OK;
@@ -174,6 +224,7 @@ int32_t ctg_poseidon_new(ctg_ctx* ctx, uint32_t full_rounds, uint32_t partial_ro
   if (bytes > 48 * 1024) {
     cudaFuncSetAttribute(poseidon_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     cudaFuncSetAttribute(poseidon_compress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaFuncSetAttribute(poseidon_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   }
   *out = p;
   return CTG_OK;
