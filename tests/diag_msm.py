@@ -1,7 +1,7 @@
 """GPU diagnostic: G1 MSM over device-generated progression bases vs the discrete-log closed form,
 for several (table size, prefix, copies, c) choices.  Test tooling only."""
 import sys, os, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))   # tests/ -> repo root
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "contangle-zkcp_b200"))
 import numpy as np
 import ctg

@@ -54,6 +54,11 @@ def test_product_does_not_reference_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", "Makefile", ".rs", ".toml")):
                 txt = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in txt, os.path.join(dirpath, f)
+    # measurement / sweep scripts are not checkers either: only tests/, smoke() and bench.py's CPU legs may use oracle/
+    for f in os.listdir(os.path.join(ROOT, "tools")):
+        if f.endswith(".py"):
+            txt = open(os.path.join(ROOT, "tools", f)).read()
+            assert "from oracle" not in txt and "import oracle" not in txt, f
 
 
 def test_rust_sys_crate_binds_every_declared_symbol():

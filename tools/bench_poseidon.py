@@ -1,9 +1,11 @@
 """Bulk Poseidon timing on one B200: Merkle tree over 2^k device-resident leaves and bulk two-to-one hashes, CUDA events on
-the launching stream; the same tree through the host-buffer call (copies inside).  A bounded sample on the big-int checker
-is timed beside it.  Usage (GPU box): python tools/bench_poseidon.py [--logs 16 20 22]"""
+the launching stream; the same tree through the host-buffer call (copies inside).  Parity is tests/test_poseidon.py's job;
+the big-int checker's own speed (0.22 ms per permutation on one core) was timed there.
+Usage (GPU box): python tools/bench_poseidon.py [--logs 16 20 22]"""
 import argparse
 import json
 import os
+import random
 import sys
 import time
 
@@ -14,8 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "contangle-zkcp_b200"))
 import ctg  # noqa: E402
-from oracle import ark  # noqa: E402  (checker / CPU sample only)
-from oracle.py import poseidon as P  # noqa: E402
+from ctg import synthetic as S  # noqa: E402
 
 
 def main():
@@ -26,14 +27,16 @@ def main():
     torch.cuda.set_device(dev)
     stream = torch.cuda.current_stream()
     ctx = ctg.Context(0, stream=stream.cuda_stream)
-    p = P.random_parameters(11)
-    mds = ark.fr_mont_from_ints([v for row in p.mds for v in row]).reshape(3, 3, 8)
-    rc = ark.fr_mont_from_ints([v for row in p.ark for v in row]).reshape(len(p.ark), 3, 8)
-    pos = ctx.poseidon(p.full_rounds, p.partial_rounds, p.alpha, mds, rc)
+    rnd = random.Random(11)
+    full_rounds, partial_rounds, alpha = 8, 31, 17        # the reference's shape (circuits-ark/src/parameters.rs:226-229)
+    rounds = full_rounds + partial_rounds
+    mds = S.fr_mont([rnd.randrange(S.R_MOD) for _ in range(9)]).reshape(3, 3, 8)
+    rc = S.fr_mont([rnd.randrange(S.R_MOD) for _ in range(3 * rounds)]).reshape(rounds, 3, 8)
+    pos = ctx.poseidon(full_rounds, partial_rounds, alpha, mds, rc)
     imad_per_s, _ = ctx.imad_peak_probe()
-    sbox = bin(p.alpha).count("1") - 1 + p.alpha.bit_length() - 1
-    muls = 9 * (p.full_rounds + p.partial_rounds) + sbox * (3 * p.full_rounds + p.partial_rounds)
-    out = {"params": {"full_rounds": p.full_rounds, "partial_rounds": p.partial_rounds, "alpha": p.alpha, "fr_products_per_permutation": muls},
+    sbox = bin(alpha).count("1") - 1 + alpha.bit_length() - 1
+    muls = 9 * rounds + sbox * (3 * full_rounds + partial_rounds)
+    out = {"params": {"full_rounds": full_rounds, "partial_rounds": partial_rounds, "alpha": alpha, "fr_products_per_permutation": muls},
            "mac32_peak_per_s": imad_per_s / 2, "trees": {}}
     for lg in args.logs:
         n = 1 << lg
@@ -60,13 +63,6 @@ def main():
         out["trees"][f"2^{lg}"] = {"ms": ms, "permutations": perms, "Mperm_per_s": perms / ms / 1e3,
                                    "frac_of_mac32_peak": perms * muls * 136.0 / (ms * 1e-3) / (imad_per_s / 2),
                                    "host_buffers_ms": host_ms}
-    # bounded CPU sample on the big-int checker (single thread)
-    rows = [[i + 1, i + 2] for i in range(300)]
-    t0 = time.perf_counter()
-    for r in rows:
-        P.crh(p, r)
-    cpu = (time.perf_counter() - t0) / len(rows)
-    out["cpu_bigint_checker"] = {"ms_per_permutation": cpu * 1e3, "cores": 1, "sample": "300 two-to-one hashes"}
     print(json.dumps(out), flush=True)
 
 
