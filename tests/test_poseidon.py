@@ -1,6 +1,8 @@
 """Bulk Poseidon / ciphertext Merkle tree: csrc/poseidon.cu through the C ABI against the big-int
 duplex-sponge restatement oracle/py/poseidon.py (parity unpinned, see its header).  The CPU part pins the oracle's own
 structure: the sponge state machine against a hand-unrolled permutation, tree against paths."""
+import json
+import os
 import random
 
 import numpy as np
@@ -92,6 +94,34 @@ def test_oracle_merkle_paths_verify(n):
         P.MerkleTree(p, leaves[:n - 1] if n > 2 else leaves[:1])
 
 
+# ----------------------------------------------------------------------------- golden fixture (tests/golden/make_golden_poseidon.py)
+I = lambda h: int(h, 16)
+
+
+def _golden():
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "poseidon_bls12_381_fr.json")) as f:
+        return json.load(f)
+
+
+def _golden_params(case):
+    return P.PoseidonParameters(case["full_rounds"], case["partial_rounds"], case["alpha"], [[I(v) for v in row] for row in case["mds"]],
+                                [[I(v) for v in row] for row in case["ark"]])
+
+
+@pytest.mark.parametrize("ci", [0, 1, 2])
+def test_oracle_reproduces_golden(ci):
+    case = _golden()["cases"][ci]
+    p = _golden_params(case)
+    for h in case["hashes"]:
+        assert P.crh(p, [I(v) for v in h["inputs"]]) == I(h["digest"])
+    for t in case["trees"]:
+        tree = P.MerkleTree(p, [I(v) for v in t["leaves"]])
+        assert tree.leaf_nodes == [I(v) for v in t["leaf_nodes"]] and tree.non_leaf_nodes == [I(v) for v in t["non_leaf_nodes"]]
+        sib, path, idx = tree.generate_proof(t["path"]["leaf_index"])
+        assert sib == I(t["path"]["leaf_sibling_hash"]) and path == [I(v) for v in t["path"]["auth_path"]]
+        assert P.verify_path(p, tree.root(), I(t["leaves"][idx]), (sib, path, idx))
+
+
 # ----------------------------------------------------------------------------- GPU parity through the C ABI
 @pytest.fixture(scope="module")
 def ctx():
@@ -116,6 +146,25 @@ def test_hash_batch_matches_oracle(ctx, shape):
         got = _ints(pos.hash_batch(words))
         assert got == [P.crh(p, row) for row in rows], (shape, k)
     assert pos.hash_batch(np.zeros((0, 2, 8), dtype=np.uint32)).shape == (0, 8)
+    pos.free()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", [0, 1, 2])
+def test_gpu_reproduces_golden(ctx, ci):
+    case = _golden()["cases"][ci]
+    p = _golden_params(case)
+    pos = ctx.poseidon(p.full_rounds, p.partial_rounds, p.alpha, *_params_words(p))
+    for h in case["hashes"]:
+        words = ark.fr_mont_from_ints([I(v) for v in h["inputs"]]).reshape(1, len(h["inputs"]), 8)
+        assert _ints(pos.hash_batch(words)) == [I(h["digest"])]
+    for t in case["trees"]:
+        tree = pos.merkle_tree(ark.fr_mont_from_ints([I(v) for v in t["leaves"]]))
+        assert _ints(tree.leaf_nodes) == [I(v) for v in t["leaf_nodes"]]
+        assert _ints(tree.non_leaf_nodes) == [I(v) for v in t["non_leaf_nodes"]]
+        sib, path, idx = tree.generate_proof(t["path"]["leaf_index"])
+        assert _ints(sib) == [I(t["path"]["leaf_sibling_hash"])]
+        assert _ints(np.array(path).reshape(-1, 8)) == [I(v) for v in t["path"]["auth_path"]]
     pos.free()
 
 
