@@ -39,7 +39,7 @@ EXPORTS = [
     "ctg_proof_serialize", "ctg_proof_deserialize", "ctg_prove_partial_begin", "ctg_prove_partial_finish",
     "ctg_pk_upload_range",
     "ctg_poseidon_new", "ctg_poseidon_free", "ctg_poseidon_hash_batch", "ctg_poseidon_hash_batch_dev",
-    "ctg_poseidon_merkle_tree", "ctg_poseidon_merkle_tree_dev",
+    "ctg_poseidon_merkle_tree", "ctg_poseidon_merkle_tree_dev", "ctg_te_mul_batch", "ctg_te_mul_batch_dev",
 ]
 
 
@@ -234,6 +234,31 @@ class Context:
         self._check(load().ctg_poseidon_new(self.h, C.c_uint32(full_rounds), C.c_uint32(partial_rounds), C.c_uint32(alpha),
                                             _ptr(mds), _ptr(ark), C.byref(h)))
         return Poseidon(self, h)
+
+    def te_mul_batch(self, d, points, scalars):
+        """scalars[i] * points[i] (or * points[0] when one point is given) on -x^2 + y^2 = 1 + d x^2 y^2 over Fr (JubJub):
+        d (8,) Montgomery words, points (1 | n, 2, 8) affine Montgomery, scalars (n, 8) 256-bit integers -> (n, 2, 8)."""
+        d = np.ascontiguousarray(d, dtype=np.uint32).reshape(FR_W)
+        points = np.ascontiguousarray(points, dtype=np.uint32)
+        scalars = _arr(scalars, FR_W)
+        if points.ndim != 3 or points.shape[1:] != (2, FR_W):
+            raise CtgError("te_mul: points must be (1 | n, 2, 8) Fr words")
+        n = scalars.shape[0]
+        out = np.empty((n, 2, FR_W), dtype=np.uint32)
+        self._check(load().ctg_te_mul_batch(self.h, _ptr(d), _ptr(points), C.c_uint64(points.shape[0]), _ptr(scalars), C.c_uint64(n), _ptr(out)))
+        return out
+
+    def elgamal_encrypt_batch(self, poseidon, d, generator, pk, randomness, messages):
+        """EncryptCircuit::encrypt (circuits-ark/src/encryption.rs:154-172) for n (randomness, message) pairs under one public
+        key: c1[i] = G * r[i]; pad[i] = sponge(pk * r[i]); c2[i][j] = pad[i] + messages[i][j].  generator, pk: (2, 8) affine;
+        randomness (n, 8) integers; messages (n, chunks, 8) Montgomery -> (c1 (n, 2, 8), c2 (n, chunks, 8))."""
+        messages = np.ascontiguousarray(messages, dtype=np.uint32)
+        n, chunks = messages.shape[0], messages.shape[1]
+        c1 = self.te_mul_batch(d, np.asarray(generator, dtype=np.uint32).reshape(1, 2, FR_W), randomness)
+        shared = self.te_mul_batch(d, np.asarray(pk, dtype=np.uint32).reshape(1, 2, FR_W), randomness)
+        pad = poseidon.hash_batch(shared)
+        c2 = self.field_op(FIELD_FR, OP_ADD, messages.reshape(n * chunks, FR_W), np.repeat(pad, chunks, axis=0))
+        return c1, c2.reshape(n, chunks, FR_W)
 
     # ---- bases / MSM
     def bases_g1(self, points, copies=0, c_bits=0):

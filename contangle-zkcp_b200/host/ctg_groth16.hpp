@@ -258,4 +258,14 @@ class Poseidon {
   ctg_poseidon* p_ = nullptr;
 };
 
+// bulk JubJub scalar multiplication (c1 = G.mul(r), p_r = pk.mul(r) of encrypt(), circuits-ark/src/encryption.rs:160-165):
+// points = one shared (x, y) pair or one per scalar; scalars = 8 words each (into_repr()); returns n (x, y) pairs
+inline std::vector<ctg_fr> te_mul_batch(const Context& ctx, const ctg_fr& d, const std::vector<ctg_fr>& points_xy, const std::vector<uint32_t>& scalars) {
+  if (scalars.size() % 8 || points_xy.size() % 2) throw Error(CTG_ERR_INVALID, "te_mul: shapes");
+  const uint64_t n = scalars.size() / 8;
+  std::vector<ctg_fr> out(2 * n);
+  ctx.check(ctg_te_mul_batch(ctx.raw(), &d, points_xy.data(), points_xy.size() / 2, scalars.data(), n, out.data()));
+  return out;
+}
+
 }  // namespace ctg

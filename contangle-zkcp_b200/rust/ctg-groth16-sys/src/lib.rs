@@ -120,6 +120,10 @@ extern "C" {
                                     inner: *mut ctg_fr) -> i32;
     pub fn ctg_poseidon_merkle_tree_dev(ctx: *mut ctg_ctx, p: *const ctg_poseidon, d_leaves: *const c_void, n: u64, d_leaf_digests: *mut c_void,
                                         d_inner: *mut c_void) -> i32;
+    // bulk JubJub scalar multiplication: the group part of encrypt() / keygen() (circuits-ark/src/encryption.rs:126-137,160-165)
+    pub fn ctg_te_mul_batch(ctx: *mut ctg_ctx, d: *const ctg_fr, points: *const ctg_fr, n_points: u64, scalars: *const u32, n: u64, out: *mut ctg_fr) -> i32;
+    pub fn ctg_te_mul_batch_dev(ctx: *mut ctg_ctx, d: *const ctg_fr, d_points: *const c_void, n_points: u64, d_scalars: *const c_void, n: u64,
+                                d_out: *mut c_void) -> i32;
     // primitives, device-pointer variants, tuning knobs and harness helpers (tests / benches / ncu captures)
     pub fn ctg_ctx_set_ba_levels(ctx: *mut ctg_ctx, levels: c_int) -> i32;
     pub fn ctg_ctx_set_msm_split(ctx: *mut ctg_ctx, parts: c_int) -> i32;

@@ -307,6 +307,17 @@ int32_t ctg_poseidon_hash_batch_dev(ctg_ctx* ctx, const ctg_poseidon* p, const v
 int32_t ctg_poseidon_merkle_tree(ctg_ctx* ctx, const ctg_poseidon* p, const ctg_fr* leaves, uint64_t n, ctg_fr* leaf_digests, ctg_fr* inner);
 int32_t ctg_poseidon_merkle_tree_dev(ctg_ctx* ctx, const ctg_poseidon* p, const void* d_leaves, uint64_t n, void* d_leaf_digests, void* d_inner);
 
+/* ---- bulk scalar multiplication on a twisted Edwards curve over Fr (JubJub): the group part of hashed ElGamal ----------
+ * out[i] = scalars[i] * points[n_points == 1 ? 0 : i] on -x^2 + y^2 = 1 + d x^2 y^2 (a = -1; d a non-square, e.g. JubJub's
+ * -10240/10241), i.e. for many randomness values at once the c1 = G.mul(r), p_r = pk.mul(r), into_affine() of encrypt()
+ * (circuits-ark/src/encryption.rs:160-165) and the pk = G.mul(sk) of keygen (:126-137).  points / out: affine (x, y) pairs of
+ * Montgomery Fr images (ark_ed_on_bls12_381::EdwardsAffine field by field); scalars: 256-bit little-endian integers, 8 words
+ * each (the scalar field's into_repr(); any 256-bit value is accepted); d: Montgomery.  The identity is (0, 1).
+ * n_points must be 1 (one shared base) or n.  The ElGamal pad is then ctg_poseidon_hash_batch over the p_r pairs with k = 2 and
+ * c2 = pad + m (ctg_field_op_batch).  Points are not checked to be on the curve (arkworks does not check in mul either). */
+int32_t ctg_te_mul_batch(ctg_ctx* ctx, const ctg_fr* d, const ctg_fr* points, uint64_t n_points, const uint32_t* scalars, uint64_t n, ctg_fr* out);
+int32_t ctg_te_mul_batch_dev(ctg_ctx* ctx, const ctg_fr* d, const void* d_points, uint64_t n_points, const void* d_scalars, uint64_t n, void* d_out);
+
 #ifdef __cplusplus
 }
 #endif

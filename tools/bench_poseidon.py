@@ -63,6 +63,27 @@ def main():
         out["trees"][f"2^{lg}"] = {"ms": ms, "permutations": perms, "Mperm_per_s": perms / ms / 1e3,
                                    "frac_of_mac32_peak": perms * muls * 136.0 / (ms * 1e-3) / (imad_per_s / 2),
                                    "host_buffers_ms": host_ms}
+    # bulk JubJub scalar multiplication (the group part of encrypt()): 2^20 scalars on one shared base, device-resident
+    d_jj = S.fr_mont([(-10240 * pow(10241, -1, S.R_MOD)) % S.R_MOD])[0]
+    gen = S.fr_mont([8076246640662884909881801758704306714034609987455869804520522091855516602923,
+                     13262374693698910701929044844600465831413122818447359594527400194675274060458])
+    n = 1 << 20
+    d_gen = torch.from_numpy(gen.view(np.int32).copy()).to(dev)
+    ks = torch.randint(-(1 << 31), (1 << 31) - 1, (n, 8), device=dev, dtype=torch.int32)
+    res = torch.empty((n, 2, 8), device=dev, dtype=torch.int32)
+    import ctypes as C
+    call = lambda: ctx._check(ctg.load().ctg_te_mul_batch_dev(ctx.h, d_jj.ctypes.data_as(C.c_void_p), C.c_void_p(d_gen.data_ptr()), C.c_uint64(1),
+                                                              C.c_void_p(ks.data_ptr()), C.c_uint64(n), C.c_void_p(res.data_ptr())))
+    call()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(3):
+        call()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    out["te_mul_2^20"] = {"ms": ms, "Mscalar_mults_per_s": n / ms / 1e3}
     print(json.dumps(out), flush=True)
 
 
