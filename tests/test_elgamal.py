@@ -89,6 +89,22 @@ def test_te_mul_per_item_bases_and_small_order_points(ctx):
 
 
 @pytest.mark.gpu
+def test_te_mul_window_table_path_equals_double_and_add(ctx):
+    """From 4096 scalars on one shared base the library switches to a window table (no doublings): same points as the plain
+    double-and-add kernel (forced by passing the base once per scalar), on edge scalars and bases outside the prime subgroup."""
+    edge = [0, 1, 255, 256, 257, (1 << 256) - 1, 1 << 255, J.SUBGROUP_ORDER, J.SUBGROUP_ORDER - 1, 0xFF << 248, 0xFF00FF << 120]
+    n = 5000
+    ks = edge + [rnd.randrange(1 << 256) for _ in range(n - len(edge))]
+    odd_base = next(p for p in (J.point_from_x(x) for x in range(2, 30)) if p and J.mul(p, J.SUBGROUP_ORDER) != J.IDENTITY)
+    for base in (J.GEN, odd_base, J.IDENTITY):
+        shared = ctx.te_mul_batch(_d(), _pts([base]), _scalars(ks))
+        per_item = ctx.te_mul_batch(_d(), np.ascontiguousarray(np.broadcast_to(_pts([base]), (n, 2, 8))), _scalars(ks))
+        assert np.array_equal(shared, per_item)
+        got = _pts_back(shared[:len(edge) + 4])
+        assert got == [J.mul(base, k) for k in ks[:len(edge) + 4]]
+
+
+@pytest.mark.gpu
 def test_te_mul_other_curve_coefficient(ctx):
     """d is the caller's: another non-square coefficient gives that curve's group law."""
     d = next(v for v in range(5, 200) if pow(v, (R - 1) // 2, R) == R - 1)
