@@ -403,6 +403,18 @@ def extras(ctx, torch, dev, stream, S, args):
     pos.free()
     out["poseidon_merkle_tree"] = {"params": {"full_rounds": full_r, "partial_rounds": part_r, "alpha": alpha, "fr_products_per_permutation": fr_products},
                                    "leaves": trees}
+    # bulk JubJub scalar multiplication, the group part of encrypt() (one shared base, window table)
+    import numpy as _np
+    n = 1 << 20
+    d_jj = S.fr_mont([(-10240 * pow(10241, -1, S.R_MOD)) % S.R_MOD])[0]
+    gen = S.fr_mont([8076246640662884909881801758704306714034609987455869804520522091855516602923,
+                     13262374693698910701929044844600465831413122818447359594527400194675274060458])
+    d_gen = torch.from_numpy(gen.view(_np.int32).copy()).to(dev)
+    ks = torch.randint(-(1 << 31), (1 << 31) - 1, (n, 8), device=dev, dtype=torch.int32)
+    res = torch.empty((n, 2, 8), device=dev, dtype=torch.int32)
+    ms = ev_time(lambda: ctx.te_mul_batch_dev(d_jj, d_gen.data_ptr(), 1, ks.data_ptr(), n, res.data_ptr()), 3)
+    out["jubjub_scalar_mul_shared_base_2^20"] = {"ms": ms, "Mscalar_mults_per_s": n / ms / 1e3}
+    del ks, res
     msm = {}
     for lg in (16, 18, 20, 24):
         n = 1 << lg

@@ -248,6 +248,11 @@ class Context:
         self._check(load().ctg_te_mul_batch(self.h, _ptr(d), _ptr(points), C.c_uint64(points.shape[0]), _ptr(scalars), C.c_uint64(n), _ptr(out)))
         return out
 
+    def te_mul_batch_dev(self, d, d_points, n_points, d_scalars, n, d_out):
+        d = np.ascontiguousarray(d, dtype=np.uint32).reshape(FR_W)
+        self._check(load().ctg_te_mul_batch_dev(self.h, _ptr(d), C.c_void_p(d_points), C.c_uint64(n_points), C.c_void_p(d_scalars),
+                                                C.c_uint64(n), C.c_void_p(d_out)))
+
     def elgamal_encrypt_batch(self, poseidon, d, generator, pk, randomness, messages):
         """EncryptCircuit::encrypt (circuits-ark/src/encryption.rs:154-172) for n (randomness, message) pairs under one public
         key: c1[i] = G * r[i]; pad[i] = sponge(pk * r[i]); c2[i][j] = pad[i] + messages[i][j].  generator, pk: (2, 8) affine;

@@ -71,9 +71,7 @@ def main():
     d_gen = torch.from_numpy(gen.view(np.int32).copy()).to(dev)
     ks = torch.randint(-(1 << 31), (1 << 31) - 1, (n, 8), device=dev, dtype=torch.int32)
     res = torch.empty((n, 2, 8), device=dev, dtype=torch.int32)
-    import ctypes as C
-    call = lambda: ctx._check(ctg.load().ctg_te_mul_batch_dev(ctx.h, d_jj.ctypes.data_as(C.c_void_p), C.c_void_p(d_gen.data_ptr()), C.c_uint64(1),
-                                                              C.c_void_p(ks.data_ptr()), C.c_uint64(n), C.c_void_p(res.data_ptr())))
+    call = lambda: ctx.te_mul_batch_dev(d_jj, d_gen.data_ptr(), 1, ks.data_ptr(), n, res.data_ptr())
     call()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
