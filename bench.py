@@ -349,6 +349,14 @@ def extras_sharded(ctx, torch, dev, S, dist, rank, world):
     return out
 
 
+def _np_rand_fr(S, n):
+    """n seeded Montgomery images below the modulus (top word < 2^30)."""
+    import numpy as np
+    w = np.random.default_rng(1234).integers(0, 1 << 32, size=(n, 8), dtype=np.uint64).astype(np.uint32)
+    w[:, 7] &= 0x3FFFFFFF
+    return w
+
+
 def extras(ctx, torch, dev, stream, S, args):
     """Other rows of the metric (reported, not the headline): NTT GB/s, MSM size sweep, Groth16 prove ms."""
     out = {}
@@ -400,6 +408,19 @@ def extras(ctx, torch, dev, stream, S, args):
         trees[f"2^{lg}"] = {"ms": ms, "Mpermutations_per_s": (2 * n - 1) / ms / 1e3,
                             "frac_of_mac32_peak": (2 * n - 1) * fr_products * 136.0 / (ms * 1e-3) / mac_peak}
         del leaves, dig, inner
+    # cpu_baseline leg for this row: the same tree over 2^16 leaves on the host cores (oracle/c, all threads), and equality
+    from oracle import ark as _ark_pos  # checker / cpu_baseline leg only
+    host_leaves = _np_rand_fr(S, 1 << 16)
+    mds_w = S.fr_mont([prnd.randrange(S.R_MOD) for _ in range(9)]).reshape(3, 3, 8)
+    rc_w = S.fr_mont([prnd.randrange(S.R_MOD) for _ in range(3 * (full_r + part_r))]).reshape(full_r + part_r, 3, 8)
+    pos2 = ctx.poseidon(full_r, part_r, alpha, mds_w, rc_w)
+    gpu_tree = pos2.merkle_tree(host_leaves)
+    t0 = time.perf_counter()
+    cpu_leaf, cpu_inner = _ark_pos.poseidon_merkle_tree(full_r, part_r, alpha, mds_w, rc_w, host_leaves)
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    pos2.free()
+    trees["2^16"].update({"cpu_port_ms": cpu_ms, "cpu_cores": _ark_pos.lib().ark_get_threads(), "gpu_over_cpu": cpu_ms / trees["2^16"]["ms"],
+                          "gpu_matches_cpu": bool((gpu_tree.leaf_nodes == cpu_leaf).all() and (gpu_tree.non_leaf_nodes == cpu_inner).all())})
     pos.free()
     out["poseidon_merkle_tree"] = {"params": {"full_rounds": full_r, "partial_rounds": part_r, "alpha": alpha, "fr_products_per_permutation": fr_products},
                                    "leaves": trees}

@@ -362,3 +362,24 @@ def pk_from_py(pk):
         d[k] = g1_from_py(getattr(pk, k))
     d["b_g2_query"] = g2_from_py(pk.b_g2_query)
     return d
+
+
+# ------------------------------------------------------------ Poseidon / Merkle tree (oracle/py/poseidon.py holds the conventions)
+def poseidon_hash_batch(full_rounds, partial_rounds, alpha, mds, rc, inputs):
+    """inputs (n, k, 8) Montgomery -> (n, 8): CRH of each row (fresh sponge, absorb k, squeeze 1)."""
+    mds, rc, inputs = _c(mds, FR_W), _c(rc, FR_W), _c(inputs, FR_W)
+    n, k = inputs.shape[0], inputs.shape[1]
+    out = np.empty((n, FR_W), dtype=np.uint32)
+    lib().ark_poseidon_hash_batch(int(full_rounds), int(partial_rounds), C.c_uint64(alpha), _p(mds), _p(rc), _p(inputs), C.c_uint64(n), C.c_uint64(k), _p(out))
+    return out
+
+
+def poseidon_merkle_tree(full_rounds, partial_rounds, alpha, mds, rc, leaves):
+    """leaves (n, 8) -> (leaf_nodes (n, 8), non_leaf_nodes (n - 1, 8) in heap order)."""
+    mds, rc, leaves = _c(mds, FR_W), _c(rc, FR_W), _c(leaves, FR_W)
+    n = leaves.shape[0]
+    assert n >= 2 and n & (n - 1) == 0
+    leaf_nodes = np.empty((n, FR_W), dtype=np.uint32)
+    inner = np.empty((n - 1, FR_W), dtype=np.uint32)
+    lib().ark_poseidon_merkle_tree(int(full_rounds), int(partial_rounds), C.c_uint64(alpha), _p(mds), _p(rc), _p(leaves), C.c_uint64(n), _p(leaf_nodes), _p(inner))
+    return leaf_nodes, inner

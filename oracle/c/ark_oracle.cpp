@@ -526,4 +526,52 @@ void ark_lagrange_coeffs(int log_n, const Fr* tau, Fr* out) {
   Fr inv = acc.inv();
   for (size_t i = n; i-- > 0;) { out[i] = out[i] * (inv * pref[i]); inv = inv * den[i]; }
 }
+// ---- Poseidon (ark-sponge 0.3.0 PoseidonSponge, rate 2 / capacity 1) and the ciphertext Merkle tree -- the CPU side of
+// SURVEY 8(f) row 4 (circuits-ark/src/sample_entries.rs:127-134, encryption.rs:154-172); mirrors oracle/py/poseidon.py, which
+// holds the conventions, with machine-word Montgomery arithmetic and all host threads (rayon would do the same per level).
+struct PoseidonCfg { int full, partial; u64 alpha; const Fr* mds; const Fr* ark; };
+static inline Fr poseidon_sbox(const Fr& x, u64 alpha) {   // x^alpha, square-and-multiply from the top set bit (alpha >= 1)
+  Fr acc = x;
+  for (int b = 62 - __builtin_clzll(alpha); b >= 0; b--) { acc = acc.sqr(); if ((alpha >> b) & 1) acc = acc * x; }
+  return acc;
+}
+static void poseidon_permute(const PoseidonCfg& c, Fr st[3]) {
+  const int half = c.full / 2, rounds = c.full + c.partial;
+  for (int r = 0; r < rounds; r++) {
+    for (int i = 0; i < 3; i++) st[i] = st[i] + c.ark[3 * r + i];
+    if (r < half || r >= half + c.partial) { for (int i = 0; i < 3; i++) st[i] = poseidon_sbox(st[i], c.alpha); }
+    else st[0] = poseidon_sbox(st[0], c.alpha);
+    Fr nw[3];
+    for (int i = 0; i < 3; i++) nw[i] = c.mds[3 * i] * st[0] + c.mds[3 * i + 1] * st[1] + c.mds[3 * i + 2] * st[2];
+    for (int i = 0; i < 3; i++) st[i] = nw[i];
+  }
+}
+// fresh sponge, absorb k elements, squeeze one
+static Fr poseidon_crh(const PoseidonCfg& c, const Fr* in, u64 k) {
+  Fr st[3] = {Fr::zero(), Fr::zero(), Fr::zero()};
+  u64 pos = 0;
+  for (u64 e = 0; e < k; e++) {
+    if (pos == 2) { poseidon_permute(c, st); pos = 0; }
+    st[pos] = st[pos] + in[e];
+    pos++;
+  }
+  poseidon_permute(c, st);
+  return st[0];
+}
+void ark_poseidon_hash_batch(int full, int partial, u64 alpha, const Fr* mds, const Fr* ark, const Fr* in, u64 n, u64 k, Fr* out) {
+  ensure_init();
+  PoseidonCfg c{full, partial, alpha, mds, ark};
+  parallel_chunks(n, [&](size_t lo, size_t hi) { for (size_t i = lo; i < hi; i++) out[i] = poseidon_crh(c, in + i * k, k); });
+}
+void ark_poseidon_merkle_tree(int full, int partial, u64 alpha, const Fr* mds, const Fr* ark, const Fr* leaves, u64 n, Fr* leaf_nodes, Fr* non_leaf) {
+  ensure_init();
+  PoseidonCfg c{full, partial, alpha, mds, ark};
+  parallel_chunks(n, [&](size_t lo, size_t hi) { for (size_t i = lo; i < hi; i++) leaf_nodes[i] = poseidon_crh(c, leaves + i, 1); });
+  const Fr* children = leaf_nodes;
+  for (u64 width = n / 2; width >= 1; width /= 2) {
+    Fr* parents = non_leaf + (width - 1);
+    parallel_chunks(width, [&](size_t lo, size_t hi) { for (size_t i = lo; i < hi; i++) parents[i] = poseidon_crh(c, children + 2 * i, 2); });
+    children = parents;
+  }
+}
 }

@@ -94,6 +94,21 @@ def test_oracle_merkle_paths_verify(n):
         P.MerkleTree(p, leaves[:n - 1] if n > 2 else leaves[:1])
 
 
+@pytest.mark.parametrize("shape", [(8, 31, 17), (4, 3, 5), (2, 5, 2), (4, 0, 3)])
+def test_oracle_c_matches_oracle_py(shape):
+    """oracle/c (machine words, threads: the timed CPU baseline and the checker at large sizes) against the big-int restatement."""
+    p = P.random_parameters(40 + shape[2], *shape)
+    mds, rc = _params_words(p)
+    for k in (1, 2, 3, 5):
+        rows = [[rnd.randrange(R) for _ in range(k)] for _ in range(12)] + [[0] * k, [R - 1] * k]
+        words = ark.fr_mont_from_ints([v for row in rows for v in row]).reshape(len(rows), k, 8)
+        assert _ints(ark.poseidon_hash_batch(*shape, mds, rc, words)) == [P.crh(p, row) for row in rows]
+    leaves = [rnd.randrange(R) for _ in range(32)]
+    leaf_nodes, inner = ark.poseidon_merkle_tree(*shape, mds, rc, ark.fr_mont_from_ints(leaves))
+    want = P.MerkleTree(p, leaves)
+    assert _ints(leaf_nodes) == want.leaf_nodes and _ints(inner) == want.non_leaf_nodes
+
+
 # ----------------------------------------------------------------------------- golden fixture (tests/golden/make_golden_poseidon.py)
 I = lambda h: int(h, 16)
 
@@ -183,6 +198,20 @@ def test_merkle_tree_matches_oracle(ctx, n):
         wsib, wpath, _ = want.generate_proof(i)
         assert _ints(sib) == [wsib] and _ints(np.array(path).reshape(-1, 8)) == wpath and idx == i
         assert P.verify_path(p, _ints(tree.root())[0], leaves[i], (wsib, wpath, i))
+    pos.free()
+
+
+@pytest.mark.gpu
+def test_merkle_tree_2_16_leaves_node_by_node(ctx):
+    """Both kernels (one thread per hash on the wide levels, four lanes per hash on the narrow ones) against oracle/c on every node."""
+    n = 1 << 16
+    p = P.random_parameters(8)
+    mds, rc = _params_words(p)
+    pos = ctx.poseidon(p.full_rounds, p.partial_rounds, p.alpha, mds, rc)
+    leaves = ark.random_fr_mont(n, 10)
+    tree = pos.merkle_tree(leaves)
+    leaf_nodes, inner = ark.poseidon_merkle_tree(p.full_rounds, p.partial_rounds, p.alpha, mds, rc, leaves)
+    assert np.array_equal(tree.leaf_nodes, leaf_nodes) and np.array_equal(tree.non_leaf_nodes, inner)
     pos.free()
 
 
