@@ -123,6 +123,21 @@ def _golden_params(case):
                                 [[I(v) for v in row] for row in case["ark"]])
 
 
+def test_golden_generator_is_deterministic(tmp_path, monkeypatch):
+    """Re-running tests/golden/make_golden_poseidon.py reproduces the committed fixture byte for byte."""
+    import importlib.util
+    here = os.path.dirname(os.path.abspath(__file__))
+    spec = importlib.util.spec_from_file_location("make_golden_poseidon", os.path.join(here, "golden", "make_golden_poseidon.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    real_join = os.path.join
+    target = str(tmp_path / "poseidon_bls12_381_fr.json")
+    monkeypatch.setattr(mod.os.path, "join", lambda *a: target if a[-1] == "poseidon_bls12_381_fr.json" else real_join(*a))
+    mod.main()
+    with open(target, "rb") as f, open(real_join(here, "golden", "poseidon_bls12_381_fr.json"), "rb") as g:
+        assert f.read() == g.read()
+
+
 @pytest.mark.parametrize("ci", [0, 1, 2])
 def test_oracle_reproduces_golden(ci):
     case = _golden()["cases"][ci]
