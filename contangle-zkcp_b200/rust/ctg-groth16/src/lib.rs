@@ -8,6 +8,7 @@
 //! Synthesis runs on the CPU exactly as in ark-groth16 0.3.0 prover.rs (OptimizationGoal::Constraints,
 //! finalize, to_matrices); r then s are drawn with Fr::rand; only the arithmetic after synthesis is offloaded.
 mod pack;
+pub mod witness;
 
 use ark_bls12_381::{Bls12_381, Fr};
 use ark_groth16::{Proof, ProvingKey, VerifyingKey};
