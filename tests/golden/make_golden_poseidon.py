@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Generates tests/golden/poseidon_bls12_381_fr.json with the big-int restatement oracle/py/poseidon.py: frozen parameters,
-sponge digests and Merkle trees that the CUDA kernels (and the restatement itself, after any edit) are checked against.
+sponge digests, Merkle trees, JubJub multiples and hashed-ElGamal ciphertexts that the CUDA kernels (and the restatement itself, after any edit) are checked against.
 
 The reference holds no hash value for this path and cannot be run here (no Rust; ark-sponge / ark-crypto-primitives are not
 in the tree), so the fixture freezes OUR restatement of ark-sponge 0.3.0's conventions: parity stays unpinned.  The constants
@@ -17,6 +17,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from oracle.py import bls12_381 as B  # noqa: E402
+from oracle.py import jubjub as J  # noqa: E402
 from oracle.py import poseidon as P  # noqa: E402
 
 H = lambda x: format(x, "x")
@@ -42,9 +43,24 @@ def main():
                           "path": {"leaf_index": idx, "leaf_sibling_hash": H(sib), "auth_path": [H(v) for v in path]}})
         cases.append({"full_rounds": full, "partial_rounds": partial, "alpha": alpha, "mds": [[H(v) for v in row] for row in p.mds],
                       "ark": [[H(v) for v in row] for row in p.ark], "hashes": hashes, "trees": trees})
+    # hashed ElGamal on JubJub under the first parameter set (oracle/py/jubjub.py): key pair, scalar multiples, ciphertexts
+    p0 = P.random_parameters(1, 8, 31, 17)
+    sk = rnd.randrange(J.SUBGROUP_ORDER)
+    pk = J.keygen(sk)
+    pt = lambda q: [H(q[0]), H(q[1])]
+    multiples = [{"k": H(k), "point": pt(J.mul(J.GEN, k))} for k in
+                 (0, 1, 2, J.SUBGROUP_ORDER - 1, J.SUBGROUP_ORDER, (1 << 256) - 1, rnd.randrange(1 << 256), rnd.randrange(J.SUBGROUP_ORDER))]
+    ciphertexts = []
+    for chunks in (1, 4):
+        r = rnd.randrange(J.SUBGROUP_ORDER)
+        msg = [rnd.randrange(R) for _ in range(chunks)]
+        c1, c2 = J.encrypt(p0, pk, msg, r)
+        ciphertexts.append({"r": H(r), "msg": [H(m) for m in msg], "c1": pt(c1), "c2": [H(c) for c in c2]})
+    elgamal = {"d": H(J.D), "generator": pt(J.GEN), "subgroup_order": H(J.SUBGROUP_ORDER), "sk": H(sk), "pk": pt(pk),
+               "poseidon_case": 0, "multiples_of_generator": multiples, "ciphertexts": ciphertexts}
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "poseidon_bls12_381_fr.json")
     with open(path, "w") as f:
-        json.dump({"field": "BLS12-381 Fr", "modulus": H(R), "cases": cases}, f, indent=0, sort_keys=True)
+        json.dump({"field": "BLS12-381 Fr", "modulus": H(R), "cases": cases, "elgamal": elgamal}, f, indent=0, sort_keys=True)
         f.write("\n")
     print("wrote", path, os.path.getsize(path), "bytes")
 

@@ -1,5 +1,7 @@
 """Bulk JubJub scalar multiplication and hashed-ElGamal encryption: csrc/edwards.cu (+ poseidon.cu) through
 the C ABI against the big-int restatement oracle/py/jubjub.py (affine unified law; the kernel uses extended coordinates)."""
+import json
+import os
 import random
 
 import numpy as np
@@ -49,6 +51,35 @@ def test_oracle_elgamal_round_trip():
     cipher = J.encrypt(p, pk, msg, rnd.randrange(J.SUBGROUP_ORDER))
     assert J.decrypt(p, cipher, sk) == msg
     assert J.decrypt(p, cipher, (sk + 1) % J.SUBGROUP_ORDER) != msg
+
+
+# ----------------------------------------------------------------------------- golden fixture (tests/golden/make_golden_poseidon.py)
+I = lambda h: int(h, 16)
+
+
+def _golden():
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "poseidon_bls12_381_fr.json")) as f:
+        g = json.load(f)
+    case = g["cases"][g["elgamal"]["poseidon_case"]]
+    params = P.PoseidonParameters(case["full_rounds"], case["partial_rounds"], case["alpha"], [[I(v) for v in row] for row in case["mds"]],
+                                  [[I(v) for v in row] for row in case["ark"]])
+    return g["elgamal"], params
+
+
+def _pt(h):
+    return (I(h[0]), I(h[1]))
+
+
+def test_oracle_reproduces_elgamal_golden():
+    e, params = _golden()
+    assert I(e["d"]) == J.D and _pt(e["generator"]) == J.GEN and I(e["subgroup_order"]) == J.SUBGROUP_ORDER
+    assert J.keygen(I(e["sk"])) == _pt(e["pk"])
+    for m in e["multiples_of_generator"]:
+        assert J.mul(J.GEN, I(m["k"])) == _pt(m["point"])
+    for c in e["ciphertexts"]:
+        c1, c2 = J.encrypt(params, _pt(e["pk"]), [I(v) for v in c["msg"]], I(c["r"]))
+        assert c1 == _pt(c["c1"]) and c2 == [I(v) for v in c["c2"]]
+        assert J.decrypt(params, (c1, c2), I(e["sk"])) == [I(v) for v in c["msg"]]
 
 
 # ----------------------------------------------------------------------------- GPU parity through the C ABI
@@ -135,6 +166,23 @@ def test_elgamal_encrypt_batch_matches_oracle_and_decrypts(ctx):
         got = (c1[i], c2[i * chunks:(i + 1) * chunks])
         assert got == want
         assert J.decrypt(p, got, sk) == msgs[i]
+    pos.free()
+
+
+@pytest.mark.gpu
+def test_gpu_reproduces_elgamal_golden(ctx):
+    e, p = _golden()
+    ks = [I(m["k"]) for m in e["multiples_of_generator"]] + [I(e["sk"])]
+    got = _pts_back(ctx.te_mul_batch(_d(), _pts([_pt(e["generator"])]), _scalars(ks)))
+    assert got == [_pt(m["point"]) for m in e["multiples_of_generator"]] + [_pt(e["pk"])]
+    mds = ark.fr_mont_from_ints([v for row in p.mds for v in row]).reshape(3, 3, 8)
+    rc = ark.fr_mont_from_ints([v for row in p.ark for v in row]).reshape(len(p.ark), 3, 8)
+    pos = ctx.poseidon(p.full_rounds, p.partial_rounds, p.alpha, mds, rc)
+    for c in e["ciphertexts"]:
+        msg = ark.fr_mont_from_ints([I(v) for v in c["msg"]]).reshape(1, len(c["msg"]), 8)
+        c1, c2 = ctx.elgamal_encrypt_batch(pos, _d(), _pts([_pt(e["generator"])])[0], _pts([_pt(e["pk"])])[0], _scalars([I(c["r"])]), msg)
+        assert _pts_back(c1) == [_pt(c["c1"])]
+        assert ark.fr_ints_from_mont(c2.reshape(-1, 8)) == [I(v) for v in c["c2"]]
     pos.free()
 
 
