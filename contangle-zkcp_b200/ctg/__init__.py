@@ -659,3 +659,38 @@ def proof_from_bytes(data, check_subgroup=True):
     if load().ctg_proof_deserialize(C.c_void_p(raw.ctypes.data), int(bool(check_subgroup)), _ptr(out)) != 0:
         raise CtgError("proof_from_bytes: invalid encoding (arkworks: SerializationError::InvalidData)")
     return out[:G1_W].copy(), out[G1_W:G1_W + G2_W].copy(), out[G1_W + G2_W:].copy()
+
+
+# ---- the reference's own Poseidon parameter set -----------------------------------------------------------
+R_MOD_FR = 0x73EDA753299D7D483339D80809A1D80553BDA402FFFE5BFEFFFFFFFF00000001
+
+
+def _fr_from_str(dec):
+    """ark-ff 0.3 FromStr for a prime field: the decimal digits are accumulated IN the field (res = res * 10 + digit), which
+    reduces numbers larger than the modulus -- the reference's table holds 377-bit decimals (circuits-ark/src/poseidon.rs:18-33)."""
+    if not dec or not dec.isdigit() or (dec[0] == "0" and len(dec) > 1):
+        raise CtgError("from_str: not a decimal field element")
+    acc = 0
+    for ch in dec:
+        acc = (acc * 10 + ord(ch) - 48) % R_MOD_FR
+    return acc
+
+
+def _fr_mont_words(vals):
+    buf = b"".join(((v % R_MOD_FR) * (1 << 256) % R_MOD_FR).to_bytes(32, "little") for v in vals)
+    return np.frombuffer(buf, dtype=np.uint32).reshape(len(vals), FR_W).copy()
+
+
+def poseidon_reference_params():
+    """get_poseidon_params::<JubJub>(2) of the reference (circuits-ark/src/poseidon.rs:13-41): the P1 table of
+    circuits-ark/src/parameters.rs:12-229 (rate 2, alpha 17, 8 full + 31 partial rounds) parsed into BLS12-381 Fr as
+    Fr::from_str does.  Returns (full_rounds, partial_rounds, alpha, mds (3, 3, 8), ark (39, 3, 8)) -- Montgomery words,
+    ready for Context.poseidon(*poseidon_reference_params())."""
+    import json
+    with open(os.path.join(_HERE, "data", "poseidon_bls12_381_rate2.json")) as f:
+        d = json.load(f)
+    if d["rate"] != 2:
+        raise CtgError("poseidon_reference_params: the device sponge is rate 2 / capacity 1")
+    mds = _fr_mont_words([_fr_from_str(v) for row in d["mds"] for v in row]).reshape(3, 3, FR_W)
+    ark = _fr_mont_words([_fr_from_str(v) for row in d["ark"] for v in row]).reshape(len(d["ark"]), 3, FR_W)
+    return int(d["full_rounds"]), int(d["partial_rounds"]), int(d["alpha"]), mds, ark

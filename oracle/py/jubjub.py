@@ -101,3 +101,51 @@ def decrypt(params, cipher, sk):
 def selfcheck():
     assert on_curve(GEN) and mul(GEN, SUBGROUP_ORDER) == IDENTITY and mul(GEN, 1) == GEN
     assert pow(D, (R_MOD - 1) // 2, R_MOD) == R_MOD - 1, "d must be a non-square (complete addition law)"
+
+
+# ---- ark-serialize 0.3 canonical form of a twisted Edwards affine point (ark-ec 0.3.0 twisted_edwards_extended.rs, restated):
+#   serialize   : the identity is x = 0 with no flag; otherwise x (32 bytes little-endian canonical) with EdwardsFlags in the top
+#                 bit of the last byte: 0x80 = Positive (y > -y as integers), 0 = Negative (the default flag).  PINNED by the
+#                 reference: ALICE_PK has the bit set, and only the root with y > -y lies in the prime-order subgroup, which the
+#                 reference's test_public_key_decode (circuits-ark/src/utils.rs:117-121) requires by unwrapping the decode
+#   deserialize : x == 0 -> identity; else get_point_from_x(x, greatest = positive) (y^2 = (1 - a x^2) / (1 - d x^2), the larger
+#                 root when greatest), InvalidData if no root or if the point is outside the prime-order subgroup
+# Reference call sites: ark_from_bytes::<JubJub> / ark_to_bytes on the ElGamal keys (circuits-ark/src/utils.rs:12-22, :117-121);
+# the only key bytes the reference holds are ALICE_PK / ALICE_SK (circuits-ark/src/utils.rs:114-115).
+def point_compress(pt):
+    x, y = pt
+    if pt == IDENTITY:
+        return (0).to_bytes(32, "little")
+    raw = bytearray(x.to_bytes(32, "little"))
+    if y > (R_MOD - y) % R_MOD:
+        raw[31] |= 0x80
+    return bytes(raw)
+
+
+def point_decompress(data, d=D, check_subgroup=True):
+    """-> affine point, or None where arkworks returns SerializationError::InvalidData."""
+    if len(data) != 32:
+        return None
+    negative = not bool(data[31] & 0x80)
+    x = int.from_bytes(bytes(data[:31]) + bytes([data[31] & 0x7F]), "little")
+    if x >= R_MOD:
+        return None
+    if x == 0:
+        return IDENTITY
+    p = point_from_x(x, d)
+    if p is None:
+        return None
+    y = p[1]
+    ny = (R_MOD - y) % R_MOD
+    big, small = (y, ny) if y > ny else (ny, y)
+    p = (x, small if negative else big)
+    if check_subgroup and mul(p, SUBGROUP_ORDER, d) != IDENTITY:
+        return None
+    return p
+
+
+def scalar_from_bytes(data):
+    """ark_from_bytes::<Fr> of 32 little-endian bytes: the integer, or None if it is not below the modulus (the reference decodes
+    ALICE_SK as ark_bls12_381::Fr, circuits-ark/src/utils.rs:123-127)."""
+    v = int.from_bytes(data, "little")
+    return v if v < R_MOD else None
