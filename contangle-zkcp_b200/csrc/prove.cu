@@ -144,6 +144,7 @@ static int32_t make_bases(ctg_ctx* ctx, Bases& out, int group, uint64_t n, int c
   out.n = n;
   out.plan = msm_make_plan(n, copies, c_bits, sizeof(A));
   out.pts = nullptr;
+  if (n * (uint64_t)out.plan.copies >= (1ull << 31)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: query length * precomputed copies must be < 2^31 (ask for fewer copies)");
   size_t bytes = (size_t)out.plan.copies * (n ? n : 1) * sizeof(A);
   cudaError_t e = cudaMalloc(&out.pts, bytes);
   if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, CTG_ERR_OOM, "bases: cudaMalloc failed (try fewer precomputed copies)"); }
@@ -250,7 +251,12 @@ int32_t r1cs_upload(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, const c
   for (int k = 0; k < 3; k++) {
     const ctg_csr* m = mats[k];
     if (!m || !m->row_ptr) { ctx->last_error = "r1cs_upload: null matrix"; return cleanup(CTG_ERR_INVALID); }
+    // the SpMV kernel trusts the structure: row_ptr[0] = 0, non-decreasing, row_ptr[nc] = nnz entries in col / val
+    if (m->row_ptr[0] != 0) { ctx->last_error = "r1cs_upload: row_ptr[0] must be 0"; return cleanup(CTG_ERR_INVALID); }
+    for (uint64_t i = 0; i < nc; i++)
+      if (m->row_ptr[i + 1] < m->row_ptr[i]) { ctx->last_error = "r1cs_upload: row_ptr must be non-decreasing"; return cleanup(CTG_ERR_INVALID); }
     const uint64_t nnz = m->row_ptr[nc];
+    if (nnz && (!m->col || !m->val)) { ctx->last_error = "r1cs_upload: null col / val arrays"; return cleanup(CTG_ERR_INVALID); }
     r->nnz[k] = nnz;
     for (uint64_t i = 0; i < nnz; i++)
       if (m->col[i] >= ni + nw) { ctx->last_error = "r1cs_upload: column index out of range"; return cleanup(CTG_ERR_INVALID); }

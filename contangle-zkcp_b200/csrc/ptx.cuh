@@ -2,7 +2,9 @@
 //
 // On the device every helper is one PTX instruction (add.cc / madc.lo.cc / madc.hi.cc ...);
 // ptxas pairs `mad.lo.cc` + `madc.hi.cc` on the same operands into one IMAD.WIDE.U32(.X)
-// on the FMA pipe, so a 32x32->64 multiply-accumulate costs one issue slot.  When the
+// on the FMA pipe; that instruction occupies TWO issue slots of the pipe (measured:
+// profiles/r01_pipe_probe.txt), so a 32x32->64 multiply-accumulate costs two IMAD slots
+// whichever way it is written -- the MAC32 peak is half the IMAD issue rate.  When the
 // header is compiled for the host (g++ or the host pass of nvcc) the same helpers are
 // emulated with an explicit carry word so the field/curve code above them can be unit
 // tested without a GPU (tests/test_device_math_host.py).

@@ -112,6 +112,9 @@ struct DevBuf {  // frees on scope exit
 // column sums of one matrix: transposes the index on the host (counting sort by column), gathers on the device
 static int32_t qap_columns(ctg_ctx* ctx, const ctg_csr* M, uint64_t nc, uint64_t ni, uint64_t m, const Fr* d_L, int is_a, Fr* d_out, cudaStream_t st) {
   if (!M || !M->row_ptr) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: null matrix");
+  if (M->row_ptr[0] != 0) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: row_ptr[0] must be 0");
+  for (uint64_t i = 0; i < nc; i++)
+    if (M->row_ptr[i + 1] < M->row_ptr[i]) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: row_ptr must be non-decreasing");
   const uint64_t nnz = M->row_ptr[nc];
   if (nnz >= (1ull << 32)) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: more than 2^32 - 1 non-zeros in one matrix");
   if (nnz && (!M->col || !M->val)) return fail(ctx, CTG_ERR_INVALID, "generate_parameters: null matrix arrays");

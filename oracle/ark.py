@@ -192,6 +192,24 @@ def fq_sub(a, b): return _binop("ark_fq_sub_batch", a, b, FQ_W)
 def fq2_mul(a, b): return _binop("ark_fq2_mul_batch", a, b, 2 * FQ_W)
 
 
+def fr_sqr(a):
+    a = _c(a, FR_W); out = np.empty_like(a)
+    lib().ark_fr_sqr_batch(_p(a), _p(out), C.c_uint64(a.shape[0])); return out
+
+
+def fq_sqr(a):
+    a = _c(a, FQ_W); out = np.empty_like(a)
+    lib().ark_fq_sqr_batch(_p(a), _p(out), C.c_uint64(a.shape[0])); return out
+
+
+def fr_poly_eval(coeffs_mont, points_mont):
+    """sum_i coeffs[i] * x^i at each x of points (Horner, one host thread per point); Montgomery in and out."""
+    coeffs_mont, points_mont = _c(coeffs_mont, FR_W), _c(points_mont, FR_W)
+    out = np.empty_like(points_mont)
+    lib().ark_fr_poly_eval(_p(coeffs_mont), C.c_uint64(coeffs_mont.shape[0]), _p(points_mont), C.c_uint64(points_mont.shape[0]), _p(out))
+    return out
+
+
 def ntt_fr(data, inverse=False, coset=False):
     data = _c(data, FR_W).copy()
     n = data.shape[0]

@@ -133,7 +133,34 @@ template <int N, int ID> struct Fp {
     if (t[N] || geq<N>(r.v, MOD)) sub_n<N>(r.v, r.v, MOD);
     return r;
   }
-  Fp sqr() const { return *this * *this; }
+  // dedicated squaring as ark-ff's square_in_place: off-diagonal products once, doubled, plus the diagonal; then one
+  // Montgomery reduction of the 2N-limb square (N(N+1)/2 + N^2 word products instead of 2 N^2)
+  Fp sqr() const {
+    u64 t[2 * N];
+    memset(t, 0, sizeof(t));
+    for (int i = 0; i < N - 1; i++) {
+      u64 c = 0;
+      for (int j = i + 1; j < N; j++) { u128 x = (u128)v[i] * v[j] + t[i + j] + c; t[i + j] = (u64)x; c = (u64)(x >> 64); }
+      t[i + N] = c;
+    }
+    t[2 * N - 1] = t[2 * N - 2] >> 63;
+    for (int k = 2 * N - 2; k >= 2; k--) t[k] = (t[k] << 1) | (t[k - 1] >> 63);
+    t[1] <<= 1;
+    u64 c = 0;
+    for (int i = 0; i < N; i++) {
+      u128 x = (u128)v[i] * v[i] + t[2 * i] + c; t[2 * i] = (u64)x; c = (u64)(x >> 64);
+      x = (u128)t[2 * i + 1] + c; t[2 * i + 1] = (u64)x; c = (u64)(x >> 64);
+    }
+    u64 carry2 = 0;
+    for (int i = 0; i < N; i++) {
+      u64 m = t[i] * INV, cc = 0;
+      for (int j = 0; j < N; j++) { u128 x = (u128)m * MOD[j] + t[i + j] + cc; t[i + j] = (u64)x; cc = (u64)(x >> 64); }
+      u128 x = (u128)t[i + N] + cc + carry2; t[i + N] = (u64)x; carry2 = (u64)(x >> 64);
+    }
+    Fp r; memcpy(r.v, t + N, sizeof(r.v));
+    if (carry2 || geq<N>(r.v, MOD)) sub_n<N>(r.v, r.v, MOD);
+    return r;
+  }
   Fp pow(const u64* e, int n) const {
     Fp acc = one();
     for (int i = n * 64 - 1; i >= 0; i--) { acc = acc.sqr(); if ((e[i / 64] >> (i % 64)) & 1) acc = acc * *this; }
@@ -300,14 +327,20 @@ static void distribute_powers(Fr* a, size_t n, Fr g) {
 }
 static void fft_in_place(Fr* a, int log_n, Fr omega) {
   size_t n = (size_t)1 << log_n;
-  for (size_t i = 0; i < n; i++) {  // bit-reversal permutation
-    size_t j = 0;
-    for (int b = 0; b < log_n; b++) j |= ((i >> b) & 1) << (log_n - 1 - b);
-    if (i < j) std::swap(a[i], a[j]);
-  }
+  parallel_chunks(n, [&](size_t lo, size_t hi) {   // bit-reversal permutation (each swap is owned by its smaller index)
+    for (size_t i = lo; i < hi; i++) {
+      size_t j = 0;
+      for (int b = 0; b < log_n; b++) j |= ((i >> b) & 1) << (log_n - 1 - b);
+      if (i < j) std::swap(a[i], a[j]);
+    }
+  }, 4096);
   std::vector<Fr> roots(n / 2 ? n / 2 : 1);
   roots[0] = Fr::one();
-  for (size_t i = 1; i < n / 2; i++) roots[i] = roots[i - 1] * omega;
+  parallel_chunks(n / 2, [&](size_t lo, size_t hi) {   // the root table in parallel chunks, as ark-poly's roots_of_unity does
+    u64 e[1] = {lo};
+    Fr p = omega.pow(e, 1);
+    for (size_t i = lo; i < hi; i++) { roots[i] = p; p = p * omega; }
+  }, 4096);
   for (size_t m = 1; m < n; m *= 2) {
     size_t stride = n / (2 * m);
     parallel_chunks(n / 2, [&](size_t lo, size_t hi) {
@@ -487,6 +520,18 @@ void ark_fr_to_mont(const u64* canon, Fr* out, u64 n) { ensure_init(); for (u64 
 void ark_fr_from_mont(const Fr* in, u64* canon, u64 n) { ensure_init(); for (u64 i = 0; i < n; i++) in[i].to_canonical(canon + 4 * i); }
 void ark_fq_to_mont(const u64* canon, Fq* out, u64 n) { ensure_init(); for (u64 i = 0; i < n; i++) out[i] = Fq::from_canonical(canon + 6 * i); }
 void ark_fq_from_mont(const Fq* in, u64* canon, u64 n) { ensure_init(); for (u64 i = 0; i < n; i++) in[i].to_canonical(canon + 6 * i); }
+void ark_fr_sqr_batch(const Fr* a, Fr* out, u64 n) { ensure_init(); for (u64 i = 0; i < n; i++) out[i] = a[i].sqr(); }
+void ark_fq_sqr_batch(const Fq* a, Fq* out, u64 n) { ensure_init(); for (u64 i = 0; i < n; i++) out[i] = a[i].sqr(); }
+// out[j] = sum_i coeffs[i] * points[j]^i by Horner's rule, one thread per point: a check of the NTTs that is not an NTT
+void ark_fr_poly_eval(const Fr* coeffs, u64 n, const Fr* points, u64 k, Fr* out) {
+  ensure_init();
+  parallel_tasks(k, [&](size_t j) {
+    Fr acc = Fr::zero();
+    const Fr x = points[j];
+    for (u64 i = n; i-- > 0;) acc = acc * x + coeffs[i];
+    out[j] = acc;
+  });
+}
 void ark_ntt_fr(Fr* data, int log_n, int inverse, int coset) { ensure_init(); ntt_fr(data, log_n, inverse != 0, coset != 0); }
 // scalars canonical (BigInteger256 images); out affine
 void ark_msm_g1(const G1A* bases, const u64* scalars, u64 n, G1A* out) { ensure_init(); *out = to_affine(msm_ark<Fq>(bases, scalars, n)); }

@@ -448,6 +448,14 @@ def test_prove_rejects_mismatched_shapes(ctx):
     with pytest.raises(ctg.CtgError):
         ctx.upload_pk(bad, r1a["num_instance"], r1a["num_constraints"])
     dpk.free(); drb.free()
+    # malformed CSR structure is refused at upload (the SpMV kernel trusts row_ptr): non-zero start, decreasing offsets
+    for mutate in (lambda rp: rp.__setitem__(0, 1), lambda rp: rp.__setitem__(3, int(rp[4]) + 1)):
+        bad_r = dict(r1b); bad_r["a"] = dict(r1b["a"]); bad_r["a"]["row_ptr"] = r1b["a"]["row_ptr"].copy()
+        mutate(bad_r["a"]["row_ptr"])
+        with pytest.raises(ctg.CtgError):
+            ctx.upload_r1cs(bad_r)
+        with pytest.raises(ctg.CtgError):
+            ctx.generate_parameters(bad_r, S.trapdoor()[0])
 
 
 # ----------------------------------------------------------------------------- key generation

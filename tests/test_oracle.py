@@ -173,3 +173,29 @@ def test_closed_form_proof_arrays_matches_bigint_oracle():
     r, s = rnd.randrange(B.R_MOD), rnd.randrange(B.R_MOD)
     got = util.closed_form_proof_arrays(ark.r1cs_from_py(cs), dict(alpha=td.alpha, beta=td.beta, delta=td.delta, tau=td.tau), z, r, s)
     assert got == G.closed_form_proof(cs, td, z, r, s)
+
+
+def test_dedicated_squaring_equals_product():
+    """oracle/c squares with ark-ff's square_in_place schedule (off-diagonal once, doubled); it must equal a * a on edge and random values."""
+    rnd2 = random.Random(99)
+    for mod, w, sqr, mul in ((B.R_MOD, 8, ark.fr_sqr, ark.fr_mul), (B.P_MOD, 12, ark.fq_sqr, ark.fq_mul)):
+        vals = [0, 1, 2, mod - 1, mod - 2, (mod - 1) // 2, (1 << (32 * w - 1)) % mod, (1 << 64) - 1] + [rnd2.randrange(mod) for _ in range(2000)]
+        a = ark.ints_to_words(vals, w)
+        assert np.array_equal(sqr(a), mul(a, a))
+        R = 1 << (32 * w)
+        assert ark.words_to_ints(sqr(a)) == [v * v * pow(R, -1, mod) % mod for v in vals]
+
+
+@pytest.mark.parametrize("log_n", [0, 1, 5, 12])
+def test_poly_eval_is_the_transform_at_domain_points(log_n):
+    """ark_fr_poly_eval (Horner) against big-int evaluation, and against the FFT at w^j and 7 w^j: the check the large GPU NTT tests rely on."""
+    n = 1 << log_n
+    x = ark.random_fr_mont(n, 5 + log_n)
+    xi = ark.fr_ints_from_mont(x)
+    w = B.fr_root_of_unity(log_n)
+    js = sorted({0, n - 1, n // 2, 3 % n})
+    pts = [pow(w, j, B.R_MOD) for j in js] + [7 * pow(w, j, B.R_MOD) % B.R_MOD for j in js] + [12345]
+    got = ark.fr_ints_from_mont(ark.fr_poly_eval(x, ark.fr_mont_from_ints(pts)))
+    assert got == [sum(c * pow(p, i, B.R_MOD) for i, c in enumerate(xi)) % B.R_MOD for p in pts]
+    fwd, cos = ark.fr_ints_from_mont(ark.ntt_fr(x)), ark.fr_ints_from_mont(ark.ntt_fr(x, coset=True))
+    assert got[:len(js)] == [fwd[j] for j in js] and got[len(js):2 * len(js)] == [cos[j] for j in js]
