@@ -2,6 +2,7 @@
 // staging and argument checking around the kernels in ntt.cu / msm*.cu / prove.cu / fields.cu.
 // No CPU fallback exists anywhere below this file: every compute entry point launches CUDA
 // kernels on the context's device or fails with an error code.
+#include <algorithm>
 #include <cstring>
 
 #include "ctg_internal.h"
@@ -26,6 +27,18 @@ void r1cs_free(ctg_r1cs* r);
 int32_t witness_map_host(ctg_ctx* ctx, const ctg_r1cs* r, const ctg_fr* z, ctg_fr* h_out);
 int32_t prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out, ctg_timings* tm);
 uint64_t pk_num_vars(const ctg_pk* pk);
+// multi.cu
+int32_t group_create(ctg_ctx* primary, const int* device_ids, int n);
+void group_destroy(ctg_ctx* primary);
+uint64_t group_launches(const Group* g);
+int32_t group_pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, ctg_pk** out);
+void group_pk_free(ctg_ctx* ctx, ctg_pk* pk);
+int32_t group_r1cs_upload(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, const ctg_csr* const mats[3], ctg_r1cs** out);
+void group_r1cs_free(ctg_ctx* ctx, ctg_r1cs* r);
+int32_t group_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const ctg_fr* rr, const ctg_fr* ss, ctg_proof* out, ctg_timings* tm);
+int32_t group_bases_new(ctg_ctx* ctx, int group, uint64_t n, const std::function<int32_t(int, uint64_t, uint64_t, ctg_bases**)>& make, ctg_bases** out);
+void group_bases_free(ctg_ctx* ctx, ctg_bases* h);
+int32_t group_msm(ctg_ctx* ctx, const ctg_bases* bases, int group, const void* scalars, bool from_host, uint64_t n, uint32_t flags, void* out_affine, void* d_out_xyzz);
 
 int32_t fail(ctg_ctx* ctx, int32_t code, const std::string& msg) {
   if (ctx) ctx->last_error = msg;
@@ -64,6 +77,7 @@ static thread_local std::string g_null_ctx_error = "null context";
 static int32_t msm_check(ctg_ctx* ctx, const ctg_bases* bases, int group, uint64_t n) {
   if (!ctx) return CTG_ERR_INVALID;
   if (!bases) return fail(ctx, CTG_ERR_INVALID, "msm: null bases");
+  if (!bases->parts.empty()) return fail(ctx, CTG_ERR_STATE, "msm: the base table belongs to a multi-device context");
   if (bases->b.group != group) return fail(ctx, CTG_ERR_INVALID, "msm: base table is for the other group");
   if (n > bases->b.n) return fail(ctx, CTG_ERR_INVALID, "msm: more scalars than bases");
   return CTG_OK;
@@ -164,7 +178,7 @@ extern "C" {
 int32_t ctg_ctx_create(const int* device_ids, int n_devices, ctg_ctx** out) {
   if (!out) return CTG_ERR_INVALID;
   *out = nullptr;
-  if (n_devices != 1 || !device_ids) return CTG_ERR_INVALID;
+  if (n_devices < 1 || n_devices > kMaxDevices || !device_ids) return CTG_ERR_INVALID;
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return CTG_ERR_CUDA;  // no device: no fallback
   if (device_ids[0] < 0 || device_ids[0] >= count) return CTG_ERR_INVALID;
@@ -177,14 +191,20 @@ int32_t ctg_ctx_create(const int* device_ids, int n_devices, ctg_ctx** out) {
   ctx->sm_count = prop.multiProcessorCount;
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return CTG_ERR_CUDA; }
   ctx->own_stream = true;
+  if (n_devices > 1) {   // one process, several GPUs: children + worker threads + peer access (multi.cu)
+    const int32_t rc = group_create(ctx, device_ids, n_devices);
+    if (rc != CTG_OK) { ctg_ctx_destroy(ctx); return rc; }
+  }
   *out = ctx;
   return CTG_OK;
 }
+int32_t ctg_ctx_device_count(ctg_ctx* ctx) { return !ctx ? 0 : (ctx->group ? ctx->group->n : 1); }
 
 void ctg_ctx_destroy(ctg_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  if (ctx->group) group_destroy(ctx);
   for (auto& kv : ctx->domains) {
     cudaFree(kv.second.tw_fwd); cudaFree(kv.second.tw_inv); cudaFree(kv.second.gpow); cudaFree(kv.second.gpow_n); cudaFree(kv.second.gipow_n);
   }
@@ -213,7 +233,7 @@ int32_t ctg_sync(ctg_ctx* ctx) {
   CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return CTG_OK;
 }
-uint64_t ctg_launch_count(ctg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+uint64_t ctg_launch_count(ctg_ctx* ctx) { return ctx ? ctx->launches + (ctx->group ? group_launches(ctx->group) : 0) : 0; }
 int32_t ctg_last_timings(ctg_ctx* ctx, ctg_timings* out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
   *out = g_last_timings;
@@ -307,39 +327,86 @@ static int32_t bases_new(ctg_ctx* ctx, int group, uint64_t n, int copies, int c_
   return CTG_OK;
 }
 static int32_t bases_finish(ctg_ctx* ctx, ctg_bases* h) {
+  if (h->b.n == 0) { CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); return CTG_OK; }   // an empty table (e.g. a trailing shard of a tiny query)
   int32_t rc = h->b.group == 1 ? g1_precompute(ctx, h->b, ctx->stream) : g2_precompute(ctx, h->b, ctx->stream);
   if (rc != CTG_OK) return rc;
   CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return CTG_OK;
 }
-int32_t ctg_bases_upload_g1(ctg_ctx* ctx, const ctg_g1_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
-  CTG_TRY(bases_new(ctx, 1, n, copies, c_bits, out));
-  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G1Affine), cudaMemcpyDefault, ctx->stream));
+// one device: the table of one context
+static int32_t bases_upload_one(ctg_ctx* ctx, int group, const void* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  CTG_TRY(bases_new(ctx, group, n, copies, c_bits, out));
+  const size_t eb = group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * eb, cudaMemcpyDefault, ctx->stream));
   return bases_finish(ctx, *out);
 }
-int32_t ctg_bases_upload_g2(ctg_ctx* ctx, const ctg_g2_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
-  CTG_TRY(bases_new(ctx, 2, n, copies, c_bits, out));
-  if (n) CTG_CUDA(ctx, cudaMemcpyAsync((*out)->b.pts, host_points, n * sizeof(G2Affine), cudaMemcpyDefault, ctx->stream));
+static int32_t bases_progression_one(ctg_ctx* ctx, int group, const void* gen, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  CTG_TRY(bases_new(ctx, group, n, copies, c_bits, out));
+  Fr fa, fb;
+  memcpy(&fa, a, sizeof(fa)); memcpy(&fb, b, sizeof(fb));
+  if (n && group == 1) { G1Affine gg; memcpy(&gg, gen, sizeof(gg)); CTG_TRY(g1_progression_dev(ctx, gg, fa, fb, n, (G1Affine*)(*out)->b.pts, ctx->stream)); }
+  if (n && group == 2) { G2Affine gg; memcpy(&gg, gen, sizeof(gg)); CTG_TRY(g2_progression_dev(ctx, gg, fa, fb, n, (G2Affine*)(*out)->b.pts, ctx->stream)); }
   return bases_finish(ctx, *out);
+}
+// multi-device context: every device keeps the point range [n d / N, n (d + 1) / N) as an ordinary table of its own context
+static int32_t group_bases_upload(ctg_ctx* ctx, int group, const void* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (!ctx || !out) return CTG_ERR_INVALID;
+  const size_t eb = group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+  Group* g = ctx->group;
+  return group_bases_new(ctx, group, n, [=](int d, uint64_t lo, uint64_t cnt, ctg_bases** part) -> int32_t {
+    const void* src = (const char*)host_points + lo * eb;
+    return bases_upload_one(g->ctx[d], group, src, cnt, copies, c_bits, part);   // not the public entry point: ctx[0] is the multi-device context itself
+  }, out);
+}
+// P_i = (a + i b) g: device d generates its own range from a + lo b
+static int32_t group_bases_progression(ctg_ctx* ctx, int group, const void* gen, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (!ctx || !out || !gen || !a || !b) return ctx ? fail(ctx, CTG_ERR_INVALID, "progression: null argument") : CTG_ERR_INVALID;
+  Group* g = ctx->group;
+  Fr fa, fb;
+  memcpy(&fa, a, sizeof(fa)); memcpy(&fb, b, sizeof(fb));
+  return group_bases_new(ctx, group, n, [=](int d, uint64_t lo, uint64_t cnt, ctg_bases** part) -> int32_t {
+    Fr idx = Fr::zero();
+    idx.v[0] = (uint32_t)lo; idx.v[1] = (uint32_t)(lo >> 32);
+    const Fr a_d = fa + fb * idx.to_mont();
+    ctg_fr aw; memcpy(&aw, &a_d, sizeof(aw));
+    return bases_progression_one(g->ctx[d], group, gen, &aw, b, cnt, copies, c_bits, part);
+  }, out);
+}
+int32_t ctg_bases_upload_g1(ctg_ctx* ctx, const ctg_g1_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (ctx && ctx->group) return group_bases_upload(ctx, 1, host_points, n, copies, c_bits, out);
+  return bases_upload_one(ctx, 1, host_points, n, copies, c_bits, out);
+}
+int32_t ctg_bases_upload_g2(ctg_ctx* ctx, const ctg_g2_affine* host_points, uint64_t n, int copies, int c_bits, ctg_bases** out) {
+  if (ctx && ctx->group) return group_bases_upload(ctx, 2, host_points, n, copies, c_bits, out);
+  return bases_upload_one(ctx, 2, host_points, n, copies, c_bits, out);
 }
 int32_t ctg_bases_progression_g1(ctg_ctx* ctx, const ctg_g1_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {
   if (!g || !a || !b) return ctx ? fail(ctx, CTG_ERR_INVALID, "progression: null argument") : CTG_ERR_INVALID;
-  CTG_TRY(bases_new(ctx, 1, n, copies, c_bits, out));
-  G1Affine gg; Fr fa, fb;
-  memcpy(&gg, g, sizeof(gg)); memcpy(&fa, a, sizeof(fa)); memcpy(&fb, b, sizeof(fb));
-  if (n) CTG_TRY(g1_progression_dev(ctx, gg, fa, fb, n, (G1Affine*)(*out)->b.pts, ctx->stream));
-  return bases_finish(ctx, *out);
+  if (ctx && ctx->group) return group_bases_progression(ctx, 1, g, a, b, n, copies, c_bits, out);
+  return bases_progression_one(ctx, 1, g, a, b, n, copies, c_bits, out);
 }
 int32_t ctg_bases_progression_g2(ctg_ctx* ctx, const ctg_g2_affine* g, const ctg_fr* a, const ctg_fr* b, uint64_t n, int copies, int c_bits, ctg_bases** out) {
   if (!g || !a || !b) return ctx ? fail(ctx, CTG_ERR_INVALID, "progression: null argument") : CTG_ERR_INVALID;
-  CTG_TRY(bases_new(ctx, 2, n, copies, c_bits, out));
-  G2Affine gg; Fr fa, fb;
-  memcpy(&gg, g, sizeof(gg)); memcpy(&fa, a, sizeof(fa)); memcpy(&fb, b, sizeof(fb));
-  if (n) CTG_TRY(g2_progression_dev(ctx, gg, fa, fb, n, (G2Affine*)(*out)->b.pts, ctx->stream));
-  return bases_finish(ctx, *out);
+  if (ctx && ctx->group) return group_bases_progression(ctx, 2, g, a, b, n, copies, c_bits, out);
+  return bases_progression_one(ctx, 2, g, a, b, n, copies, c_bits, out);
 }
 int32_t ctg_bases_download(ctg_ctx* ctx, const ctg_bases* bases, uint64_t first, uint64_t count, void* host_points) {
   if (!ctx || !bases || !host_points) return CTG_ERR_INVALID;
+  if (!bases->parts.empty()) {   // multi-device table: points [first, first + count) of the original (copy 0) order, part by part
+    if (!ctx->group) return fail(ctx, CTG_ERR_STATE, "bases_download: the table belongs to a multi-device context");
+    if (first + count > bases->b.n) return fail(ctx, CTG_ERR_INVALID, "bases_download: range out of bounds");
+    const size_t eb = bases->b.group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
+    for (int d = 0; d < ctx->group->n; d++) {
+      const uint64_t lo = std::max<uint64_t>(first, bases->part_lo[d]), hi = std::min<uint64_t>(first + count, bases->part_lo[d + 1]);
+      if (hi <= lo) continue;
+      ctg_ctx* c = ctx->group->ctx[d];
+      const ctg_bases* part = bases->parts[d];
+      char* dst = (char*)host_points + (lo - first) * eb;
+      const uint64_t off = lo - bases->part_lo[d], cnt = hi - lo;
+      CTG_TRY(group_run_on(ctx->group, d, [=]() { return ctg_bases_download(c, part, off, cnt, dst); }));
+    }
+    return CTG_OK;
+  }
   const uint64_t total = bases->b.n * (uint64_t)bases->b.plan.copies;
   if (first + count > total) return fail(ctx, CTG_ERR_INVALID, "bases_download: range out of bounds");
   const size_t eb = bases->b.group == 1 ? sizeof(G1Affine) : sizeof(G2Affine);
@@ -347,6 +414,7 @@ int32_t ctg_bases_download(ctg_ctx* ctx, const ctg_bases* bases, uint64_t first,
 }
 void ctg_bases_free(ctg_ctx* ctx, ctg_bases* bases) {
   if (!bases) return;
+  if (!bases->parts.empty()) { if (ctx && ctx->group) { cudaStreamSynchronize(ctx->stream); group_bases_free(ctx, bases); } return; }
   if (ctx) cudaStreamSynchronize(ctx->stream);
   cudaFree(bases->b.pts);
   delete bases;
@@ -373,20 +441,24 @@ int32_t ctg_bases_plan(const ctg_bases* bases, ctg_msm_plan* out) {
 
 // ---- MSM --------------------------------------------------------------------------------------
 int32_t ctg_msm_g1_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {
+  if (ctx && ctx->group && bases) return group_msm(ctx, bases, 1, d_scalars, false, n, flags, nullptr, d_out_xyzz);
   CTG_TRY(msm_check(ctx, bases, 1, n));
   return msm_any<G1XYZZ>(ctx, bases, 1, const_cast<void*>(d_scalars), nullptr, n, flags, (G1XYZZ*)d_out_xyzz);
 }
 int32_t ctg_msm_g2_dev(ctg_ctx* ctx, const ctg_bases* bases, const void* d_scalars, uint64_t n, uint32_t flags, void* d_out_xyzz) {
+  if (ctx && ctx->group && bases) return group_msm(ctx, bases, 2, d_scalars, false, n, flags, nullptr, d_out_xyzz);
   CTG_TRY(msm_check(ctx, bases, 2, n));
   return msm_any<G2XYZZ>(ctx, bases, 2, const_cast<void*>(d_scalars), nullptr, n, flags, (G2XYZZ*)d_out_xyzz);
 }
 
 int32_t ctg_msm_g1(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_affine* out) {
   if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
+  if (ctx && ctx->group && bases) return group_msm(ctx, bases, 1, host_scalars, true, n, flags, out, nullptr);
   return msm_host<G1XYZZ, G1Affine>(ctx, bases, 1, host_scalars, n, flags, out, nullptr);
 }
 int32_t ctg_msm_g2(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g2_affine* out) {
   if (!out) return ctx ? fail(ctx, CTG_ERR_INVALID, "msm: null output") : CTG_ERR_INVALID;
+  if (ctx && ctx->group && bases) return group_msm(ctx, bases, 2, host_scalars, true, n, flags, out, nullptr);
   return msm_host<G2XYZZ, G2Affine>(ctx, bases, 2, host_scalars, n, flags, out, nullptr);
 }
 int32_t ctg_msm_g1_partial(ctg_ctx* ctx, const ctg_bases* bases, const ctg_fr* host_scalars, uint64_t n, uint32_t flags, ctg_g1_xyzz* out) {
@@ -452,6 +524,7 @@ int32_t ctg_g2_combine(ctg_ctx* ctx, const ctg_g2_xyzz* host_partials, uint32_t 
 int32_t ctg_pk_upload(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits, ctg_pk** out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
   if (c_bits != 0 && (c_bits < 2 || c_bits > 21)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: c_bits must be 0 or in [2, 21]");
+  if (ctx->group) return group_pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, out);   // one point-range shard per device
   return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, 0, 1, 1, out);
 }
 int32_t ctg_pk_upload_shard(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t num_instance, uint64_t num_constraints, int copies, int c_bits,
@@ -468,27 +541,39 @@ int32_t ctg_pk_upload_range(ctg_ctx* ctx, const ctg_pk_view* host_pk, uint64_t n
   return pk_upload(ctx, host_pk, num_instance, num_constraints, copies, c_bits, lo_num, hi_num, den, out);
 }
 void ctg_pk_free(ctg_ctx* ctx, ctg_pk* pk) {
+  if (!pk) return;
   if (ctx) cudaStreamSynchronize(ctx->stream);
+  if (!pk->parts.empty()) { if (ctx && ctx->group) group_pk_free(ctx, pk); return; }
   pk_free(pk);
 }
 int32_t ctg_r1cs_upload(ctg_ctx* ctx, uint64_t num_instance, uint64_t num_witness, uint64_t num_constraints, const ctg_csr* a, const ctg_csr* b,
                         const ctg_csr* c, ctg_r1cs** out) {
   if (!ctx || !out) return CTG_ERR_INVALID;
   const ctg_csr* mats[3] = {a, b, c};
+  if (ctx->group) return group_r1cs_upload(ctx, num_instance, num_witness, num_constraints, mats, out);
   return r1cs_upload(ctx, num_instance, num_witness, num_constraints, mats, out);
 }
 void ctg_r1cs_free(ctg_ctx* ctx, ctg_r1cs* r1cs) {
+  if (!r1cs) return;
   if (ctx) cudaStreamSynchronize(ctx->stream);
+  if (!r1cs->parts.empty()) { if (ctx && ctx->group) group_r1cs_free(ctx, r1cs); return; }
   r1cs_free(r1cs);
 }
 int32_t ctg_witness_map(ctg_ctx* ctx, const ctg_r1cs* r1cs, const ctg_fr* z, ctg_fr* h_out) {
   if (!ctx || !r1cs || !z || !h_out) return ctx ? fail(ctx, CTG_ERR_INVALID, "witness_map: null argument") : CTG_ERR_INVALID;
+  if (!r1cs->parts.empty()) r1cs = r1cs->parts[0];   // multi-device context: the witness map alone runs on the primary device
   return witness_map_host(ctx, r1cs, z, h_out);
 }
 int32_t ctg_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s, ctg_proof* out,
                   ctg_timings* timings) {
   if (!ctx) return CTG_ERR_INVALID;
   ctg_timings local;
+  if (ctx->group) {   // sharded over the context's devices; the result is the same proof
+    int32_t rc = group_prove(ctx, pk, r1cs, z, r, s, out, timings ? &local : nullptr);
+    if (rc == CTG_OK && timings) { *timings = local; g_last_timings = local; }
+    return rc;
+  }
+  if (pk && !pk->parts.empty()) return fail(ctx, CTG_ERR_STATE, "prove: the key belongs to a multi-device context");
   int32_t rc = prove(ctx, pk, r1cs, z, r, s, out, timings ? &local : nullptr);
   if (rc == CTG_OK && timings) {
     local.msm_sort_ms = g_last_timings.msm_sort_ms; local.msm_accumulate_ms = g_last_timings.msm_accumulate_ms; local.msm_reduce_ms = g_last_timings.msm_reduce_ms;
@@ -500,12 +585,20 @@ int32_t ctg_prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, const ct
 int32_t ctg_prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r1cs, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch,
                         ctg_proof* out) {
   if (!ctx || !pk || !r1cs || !z_batch || !rs_batch || !out) return ctx ? fail(ctx, CTG_ERR_INVALID, "prove_batch: null argument") : CTG_ERR_INVALID;
+  if (!pk->parts.empty() || !r1cs->parts.empty()) {   // a sharded key: the proofs of the batch run one after the other, each over all devices
+    if (!ctx->group) return fail(ctx, CTG_ERR_STATE, "prove_batch: the key belongs to a multi-device context");
+    const uint64_t m = pk_num_vars(pk);
+    for (uint32_t i = 0; i < n_proofs; i++)
+      CTG_TRY(group_prove(ctx, pk, r1cs, z_batch + (size_t)i * m, rs_batch + 2 * (size_t)i, rs_batch + 2 * (size_t)i + 1, out + i, nullptr));
+    return CTG_OK;
+  }
   return prove_batch(ctx, pk, r1cs, n_proofs, z_batch, rs_batch, out);
 }
 int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
                           ctg_proof_partial* out, ctg_timings* timings) {
   if (!ctx) return CTG_ERR_INVALID;
   ctg_timings local;
+  if ((pk_shard && !pk_shard->parts.empty()) || (r1cs && !r1cs->parts.empty())) return fail(ctx, CTG_ERR_STATE, "prove_partial: handles of a multi-device context; call ctg_prove");
   int32_t rc = prove_partial(ctx, pk_shard, r1cs, z, r, s, out, timings ? &local : nullptr);
   if (rc == CTG_OK && timings) { *timings = local; g_last_timings = local; }
   return rc;
@@ -513,11 +606,13 @@ int32_t ctg_prove_partial(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* 
 int32_t ctg_prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* z, const ctg_fr* r, const ctg_fr* s,
                                 uint32_t chain_mask, void* d_abc) {
   if (!ctx) return CTG_ERR_INVALID;
+  if ((pk_shard && !pk_shard->parts.empty()) || (r1cs && !r1cs->parts.empty())) return fail(ctx, CTG_ERR_STATE, "prove_partial: handles of a multi-device context; call ctg_prove");
   return prove_partial_begin(ctx, pk_shard, r1cs, z, r, s, chain_mask, d_abc);
 }
 int32_t ctg_prove_partial_finish(ctg_ctx* ctx, const ctg_pk* pk_shard, const ctg_r1cs* r1cs, const ctg_fr* r, const ctg_fr* s, void* d_abc,
                                  ctg_proof_partial* out) {
   if (!ctx) return CTG_ERR_INVALID;
+  if ((pk_shard && !pk_shard->parts.empty()) || (r1cs && !r1cs->parts.empty())) return fail(ctx, CTG_ERR_STATE, "prove_partial: handles of a multi-device context; call ctg_prove");
   return prove_partial_finish(ctx, pk_shard, r1cs, r, s, d_abc, out);
 }
 int32_t ctg_prove_combine(ctg_ctx* ctx, const ctg_proof_partial* partials, uint32_t k, const ctg_fr* r, const ctg_fr* s, ctg_proof* out) {

@@ -36,6 +36,7 @@ struct MsmWorkspace {
   void* chunk = nullptr;        // bucket-reduction partials
   void* result = nullptr;       // 1 XYZZ
   uint32_t* tile_sums = nullptr;  // scan scratch
+  cudaEvent_t ev_sorted = nullptr;  // recorded after the digit sort: another MSM over the same scalars and plan may reuse counts / entries
   // batched-affine tree (msm_acc.cuh): compact point arrays of the odd / even levels and their bucket offsets
   void* ba_pts[2] = {nullptr, nullptr};
   uint32_t* ba_starts[2] = {nullptr, nullptr};   // [nb + 1] each
@@ -78,10 +79,55 @@ struct ProveLane {
   cudaEvent_t ev_t[16];   // stage timers
 };
 static constexpr int kMaxLanes = 4;
+struct LaneBufs { Fr* d_z; Fr* d_abc; G1XYZZ* d_g1; G2XYZZ* d_g2; ctg_proof* d_proof; };
+}  // namespace ctg
+
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
+
+namespace ctg {
+// One host thread per device of a multi-device context: it binds the device once and then runs the jobs the
+// orchestrating (caller's) thread hands it, so that the per-device enqueue work of a sharded call proceeds in parallel.
+struct DeviceWorker {
+  int device = 0;
+  std::thread th;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::function<int32_t()> job;
+  bool has_job = false, done = false, stop = false;
+  int32_t rc = 0;
+};
+static constexpr int kMaxDevices = 8;
+static constexpr size_t kPartialBytes = 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ);   // ctg_proof_partial
+// The devices of a multi-device context (ctg_ctx_create with n_devices > 1), one process, peer access over NVLink.
+// ctx[0] is the primary context (the handle the caller holds); ctx[1..] are ordinary single-device contexts it owns.
+struct Group {
+  int n = 0;
+  ctg_ctx* ctx[kMaxDevices] = {};
+  DeviceWorker* worker[kMaxDevices] = {};
+  // sharded proof state (multi.cu / prove.cu prove_group_*)
+  Fr* d_abc[kMaxDevices] = {};        // 3 n Fr on device 0 and on every chain owner
+  Fr* d_hslice[kMaxDevices] = {};     // this device's slice of h (devices other than 0)
+  uint64_t abc_n = 0;                 // domain size the buffers above were sized for
+  void* d_parts0 = nullptr;           // device 0: n * kPartialBytes (+ proof)
+  void* h_proof = nullptr;            // pinned staging of the proof
+  cudaEvent_t ev_a[kMaxDevices] = {}, ev_part[kMaxDevices] = {}, ev_h = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+  // sharded stand-alone MSM
+  void* d_msm_parts0 = nullptr;       // device 0: n * sizeof(G2XYZZ) partial sums + result
+  void* d_scalars[kMaxDevices] = {}; size_t scalars_bytes[kMaxDevices] = {};
+  cudaEvent_t ev_msm[kMaxDevices] = {}, ev_msm_go = nullptr;
+  int chain_owner[3] = {0, 0, 0};
+};
+// runs fn(d) on every device's worker thread (device d current) and waits; returns the first non-OK code
+int32_t group_run(Group* g, const std::function<int32_t(int)>& fn);
+int32_t group_run_on(Group* g, int d, const std::function<int32_t()>& fn);
 }  // namespace ctg
 
 struct ctg_ctx {
   int device = 0;
+  ctg::Group* group = nullptr;   // non-null on the primary context of a multi-device context (ctg_ctx_create with n_devices > 1)
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   bool own_stream = true;
@@ -106,7 +152,33 @@ struct ctg_ctx {
   bool events_ready = false;
 };
 
-struct ctg_bases { ctg::Bases b; };
+struct ctg_bases {
+  ctg::Bases b;
+  // multi-device context: point-range parts, one per device (b is then unused except for group / n / plan of part 0)
+  std::vector<ctg_bases*> parts;
+  std::vector<uint64_t> part_lo;   // first point of each part
+};
+
+struct ctg_pk {
+  uint64_t m, ni, nw, n;
+  int log_n;
+  // point-range shard (multi-GPU): this key holds positions [lo, lo + cnt) of each extended query
+  int shard_index = 0, shard_count = 1;
+  uint64_t ext_lo = 0, ext_cnt = 0;  // of a_ext / b1_ext / b2_ext (m + 3 positions)
+  uint64_t l_lo = 0, l_cnt = 0;      // of l (num_witness positions)
+  uint64_t h_lo = 0, h_cnt = 0;      // of h_ext (n positions, bit-reversed order)
+  ctg::Bases a_ext, b1_ext, b2_ext, l, h_ext;
+  std::vector<ctg_pk*> parts;        // multi-device context: one shard per device (the members above are then unused)
+};
+struct ctg_r1cs {
+  uint64_t ni, nw, nc, n;
+  int log_n;
+  uint64_t* row_ptr[3];
+  uint32_t* col[3];
+  ctg::Fr* val[3];
+  uint64_t nnz[3];
+  std::vector<ctg_r1cs*> parts;      // multi-device context: a replica per device that computes witness-map chains (nullptr elsewhere)
+};
 
 // ark_groth16::ProvingKey (+ VerifyingKey) resident in HBM in arkworks' order: produced by key generation (setup.cu) or by
 // reading a circuit.zkey image (codec.cu)
@@ -144,6 +216,14 @@ namespace ctg {
   } while (0)
 
 int32_t fail(ctg_ctx* ctx, int32_t code, const std::string& msg);
+// prove.cu pieces the multi-device orchestration (multi.cu) drives
+int32_t lane_init(ctg_ctx* ctx, int idx);
+int32_t lane_bufs(ctg_ctx* ctx, ProveLane& L, uint64_t m, uint64_t n, Fr* d_abc_ext, LaneBufs* out);
+int32_t prove_group_a(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const Fr& r_m, const Fr& s_m, uint32_t chain_mask, Fr* d_abc,
+                      cudaEvent_t ev_done);
+int32_t prove_group_b(Group* g, const ctg_r1cs* r0, const Fr& r_m, const Fr& s_m);
+int32_t prove_group_c(Group* g, int d, const ctg_pk* pk, const ctg_r1cs* r);
+int32_t prove_group_d(Group* g, const Fr& r_m, const Fr& s_m, ctg_proof* out);
 int32_t ensure_scratch(ctg_ctx* ctx, size_t bytes);
 int32_t ensure_pinned(ctg_ctx* ctx, size_t bytes);
 
@@ -152,8 +232,9 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out);
 // natural order in, natural order out (ark-poly Radix2EvaluationDomain::{fft,ifft,coset_fft,coset_ifft}_in_place)
 int32_t ntt_run(ctg_ctx* ctx, Fr* d_data, int log_n, int inverse, int coset, cudaStream_t st);
 // witness-map building blocks: no bit-reversal passes (see ntt.cu)
-int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);      // natural in, natural out
-int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st);        // natural in, bit-reversed out
+// batch: that many transforms of 2^log_n elements stored back to back, one launch per pass for all of them
+int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st, uint32_t batch = 1);      // natural in, natural out
+int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d_data, int log_n, cudaStream_t st, uint32_t batch = 1);        // natural in, bit-reversed out
 
 int32_t fr_pow_table(ctg_ctx* ctx, Fr* d_out, uint64_t n, const Fr& base, const Fr& scale, cudaStream_t st);  // out[i] = scale * base^i
 Fr fr_root_of_unity(int log_n);   // generator of the 2^log_n domain (ark-poly Radix2EvaluationDomain::group_gen), Montgomery
@@ -165,10 +246,11 @@ int32_t params_alloc(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, uint64
 
 // msm_g1.cu / msm_g2.cu
 MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes);
+// batch / vec_stride / sorted: see MsmHost::run (msm.cuh)
 int32_t msm_g1_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,
-                   G1XYZZ* d_out, cudaStream_t st, float* stage_ms);
+                   G1XYZZ* d_out, cudaStream_t st, float* stage_ms, uint32_t batch = 1, uint64_t vec_stride = 0, const MsmWorkspace* sorted = nullptr);
 int32_t msm_g2_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,
-                   G2XYZZ* d_out, cudaStream_t st, float* stage_ms);
+                   G2XYZZ* d_out, cudaStream_t st, float* stage_ms, uint32_t batch = 1, uint64_t vec_stride = 0, const MsmWorkspace* sorted = nullptr);
 int32_t g1_precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st);
 int32_t g2_precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st);
 int32_t g1_to_affine_dev(ctg_ctx* ctx, const G1XYZZ* d_in, G1Affine* d_out, int count, cudaStream_t st);

@@ -53,7 +53,11 @@ __device__ __forceinline__ Fr load_scalar(const uint32_t* scalars, uint64_t i, i
 }
 
 // ---- 1. histogram -------------------------------------------------------------------------
-template <class F> __global__ void msm_count_kernel(const uint32_t* __restrict__ scalars, uint64_t n, int mont, MsmPlan plan, uint32_t* counts) {
+// blockIdx.y = index of the scalar vector in a batch (several MSMs over the SAME bases, one bucket-set group each):
+// vector p reads scalars + p * vec_stride and owns the bucket ids [p * nsets * nbuckets_per_set, (p + 1) * ...)
+template <class F> __global__ void msm_count_kernel(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t vec_stride, int mont, MsmPlan plan, uint32_t* counts) {
+  scalars += (uint64_t)blockIdx.y * vec_stride * 8;
+  const uint32_t key_base = blockIdx.y * (uint32_t)plan.nsets * plan.nbuckets_per_set;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const uint64_t n32 = (n + 31) & ~31ull;
   const unsigned lane = threadIdx.x & 31;
@@ -71,7 +75,7 @@ template <class F> __global__ void msm_count_kernel(const uint32_t* __restrict__
     for (int w = 0; w < plan.nwin; w++) {
       int32_t d = msm_signed_digit(k, plan.c, w, plan.nwin, carry);
       uint32_t key = kNoBucket;
-      if (d != 0) key = (uint32_t)(w % plan.nsets) * plan.nbuckets_per_set + (uint32_t)((d < 0 ? -d : d) - 1);
+      if (d != 0) key = key_base + (uint32_t)(w % plan.nsets) * plan.nbuckets_per_set + (uint32_t)((d < 0 ? -d : d) - 1);
       unsigned peers = __match_any_sync(0xffffffffu, key);
       if (key != kNoBucket && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&counts[key], (uint32_t)__popc(peers));
     }
@@ -136,8 +140,10 @@ template <class F> __global__ void __launch_bounds__(256) msm_scan_apply_kernel(
 }
 
 // ---- 3. scatter ---------------------------------------------------------------------------
-template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t copy_stride, int mont, MsmPlan plan,
+template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, uint64_t n, uint64_t vec_stride, uint64_t copy_stride, int mont, MsmPlan plan,
                                                       uint32_t* cursor, uint32_t* entries) {
+  scalars += (uint64_t)blockIdx.y * vec_stride * 8;
+  const uint32_t key_base = blockIdx.y * (uint32_t)plan.nsets * plan.nbuckets_per_set;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const uint64_t n32 = (n + 31) & ~31ull;
   const unsigned lane = threadIdx.x & 31;
@@ -156,7 +162,7 @@ template <class F> __global__ void msm_scatter_kernel(const uint32_t* __restrict
     for (int w = 0; w < plan.nwin; w++) {
       int32_t d = msm_signed_digit(k, plan.c, w, plan.nwin, carry);
       uint32_t key = kNoBucket;
-      if (d != 0) key = (uint32_t)(w % plan.nsets) * plan.nbuckets_per_set + (uint32_t)((d < 0 ? -d : d) - 1);
+      if (d != 0) key = key_base + (uint32_t)(w % plan.nsets) * plan.nbuckets_per_set + (uint32_t)((d < 0 ? -d : d) - 1);
       unsigned peers = __match_any_sync(0xffffffffu, key);
       int leader = __ffs(peers) - 1;
       uint32_t base = 0;
@@ -356,8 +362,11 @@ template <class F> __global__ void __launch_bounds__(32) msm_reduce_final_kernel
 
 // ---- 7. window combine --------------------------------------------------------------------------
 // sum_g 2^(c g) S_g, single thread (G - 1) * c doublings; G = 1 when every window is precomputed
-template <class F> __global__ void msm_horner_kernel(const XYZZ<F>* sets, int nsets, int c, XYZZ<F>* out) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+template <class F> __global__ void msm_horner_kernel(const XYZZ<F>* sets, int nsets, int c, XYZZ<F>* out, uint32_t batch) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;   // one thread per scalar vector of the batch
+  if (v >= batch) return;
+  sets += (size_t)v * nsets;
+  out += v;
   XYZZ<F> acc;
   copy16(acc, sets[nsets - 1]);
   for (int g = nsets - 2; g >= 0; g--) {
@@ -468,9 +477,9 @@ template <class F, int MAXC> __global__ void __launch_bounds__(128) precompute_k
 // ---- host orchestration -------------------------------------------------------------------------
 template <class F> struct MsmHost {
 
-  static int32_t ensure_ws(ctg_ctx* ctx, MsmWorkspace& ws, const MsmPlan& plan, uint64_t n, int max_threads, int ba_levels) {
-    const size_t nb = (size_t)plan.nsets * plan.nbuckets_per_set;
-    const size_t ne = (size_t)n * plan.nwin;
+  static int32_t ensure_ws(ctg_ctx* ctx, MsmWorkspace& ws, const MsmPlan& plan, uint64_t n, int max_threads, int ba_levels, uint32_t batch) {
+    const size_t nb = (size_t)batch * plan.nsets * plan.nbuckets_per_set;
+    const size_t ne = (size_t)n * plan.nwin * batch;
     if (nb + 1 > ws.cap_nb) {
       if (ws.counts) cudaFree(ws.counts);
       if (ws.cursor) cudaFree(ws.cursor);
@@ -499,7 +508,7 @@ template <class F> struct MsmHost {
     }
     // reduction scratch: chunk sums (2 * 2^16) + halving trees (main, weights, O_k: < 4 N points in all) per set
     const size_t red_n = plan.nbuckets_per_set > 65536u ? 65536u : plan.nbuckets_per_set;
-    const size_t cb = ((size_t)plan.nsets * (6 * red_n + 64) + 256) * sizeof(XYZZ<F>);
+    const size_t cb = ((size_t)batch * plan.nsets * (6 * red_n + 64) + 256) * sizeof(XYZZ<F>);
     if (cb > ws.cap_chunk_bytes) {
       if (ws.chunk) cudaFree(ws.chunk);
       CTG_CUDA(ctx, cudaMalloc(&ws.chunk, cb));
@@ -526,19 +535,25 @@ template <class F> struct MsmHost {
       }
     }
     if (!ws.result) CTG_CUDA(ctx, cudaMalloc(&ws.result, sizeof(XYZZ<Fq2>)));
+    if (!ws.ev_sorted) CTG_CUDA(ctx, cudaEventCreateWithFlags(&ws.ev_sorted, cudaEventDisableTiming));
     if (!ws.tile_sums) CTG_CUDA(ctx, cudaMalloc(&ws.tile_sums, 1025 * sizeof(uint32_t)));
     return CTG_OK;
   }
 
+  // batch > 1: `batch` scalar vectors (vector p at d_scalars + p * vec_stride elements) against the same bases; d_out[batch].
+  // One sort, one accumulate pass and one reduction serve the whole batch: vector p owns its own group of bucket sets.
+  // sorted != nullptr: another MSM over the SAME scalars and an identical plan / copy stride already sorted them into
+  // sorted->counts / ->entries (the caller has made `st` wait for sorted->ev_sorted); the digit sort is skipped.
   static int32_t run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool mont, XYZZ<F>* d_out,
-                     cudaStream_t st, float* stage_ms) {
+                     cudaStream_t st, float* stage_ms, uint32_t batch = 1, uint64_t vec_stride = 0, const MsmWorkspace* sorted = nullptr) {
     const MsmPlan& plan = bases.plan;
     if (n > bases.n) return fail(ctx, CTG_ERR_INVALID, "msm: more scalars than bases");
+    if (batch < 1) return fail(ctx, CTG_ERR_INVALID, "msm: empty batch");
     const uint64_t cstride = bases.stride ? bases.stride : bases.n;
     if (cstride * plan.copies >= (1ull << 31)) return fail(ctx, CTG_ERR_INVALID, "msm: n * copies must be < 2^31");
-    if ((uint64_t)n * plan.nwin >= (1ull << 32)) return fail(ctx, CTG_ERR_INVALID, "msm: n * windows must be < 2^32");
+    if ((uint64_t)n * plan.nwin * batch >= (1ull << 32)) return fail(ctx, CTG_ERR_INVALID, "msm: n * windows (* batch) must be < 2^32");
     if (n == 0) {
-      CTG_CUDA(ctx, cudaMemsetAsync(d_out, 0, sizeof(XYZZ<F>), st));
+      CTG_CUDA(ctx, cudaMemsetAsync(d_out, 0, (size_t)batch * sizeof(XYZZ<F>), st));
       return CTG_OK;
     }
     // accumulate launch geometry
@@ -551,10 +566,11 @@ template <class F> struct MsmHost {
     }
     const int max_blocks = ctx->sm_count * occ;
     const int max_threads = max_blocks * 128;
-    const uint32_t nb = (uint32_t)plan.nsets * plan.nbuckets_per_set;
+    if ((uint64_t)batch * plan.nsets * plan.nbuckets_per_set > 1023ull * kScanTile) return fail(ctx, CTG_ERR_INVALID, "msm: too many buckets for the scan (c or the batch too large)");
+    const uint32_t nb = batch * (uint32_t)plan.nsets * plan.nbuckets_per_set;
     const int ba_blocks = ctx->sm_count * ba_occ;
-    const int ba_levels = ctx->ba_levels >= 0 ? (ctx->ba_levels > 6 ? 6 : ctx->ba_levels) : ba_num_levels((uint64_t)n * plan.nwin, nb, (uint64_t)ba_blocks * 128, sizeof(F));
-    CTG_TRY(ensure_ws(ctx, ws, plan, n, max_threads, ba_levels));
+    const int ba_levels = ctx->ba_levels >= 0 ? (ctx->ba_levels > 6 ? 6 : ctx->ba_levels) : ba_num_levels((uint64_t)n * plan.nwin * batch, nb, (uint64_t)ba_blocks * 128, sizeof(F));
+    CTG_TRY(ensure_ws(ctx, ws, plan, n, max_threads, ba_levels, batch));
     XYZZ<F>* buckets = reinterpret_cast<XYZZ<F>*>(ws.buckets);
     XYZZ<F>* part_pt = reinterpret_cast<XYZZ<F>*>(ws.part_pt);
     XYZZ<F>* chunk = reinterpret_cast<XYZZ<F>*>(ws.chunk);
@@ -565,25 +581,33 @@ template <class F> struct MsmHost {
     }
     if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
 
-    CTG_CUDA(ctx, cudaMemsetAsync(ws.counts, 0, (size_t)(nb + 1) * sizeof(uint32_t), st));
-    const int dig_blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx->sm_count * 8);
-    msm_count_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, mont ? 1 : 0, plan, ws.counts);
-    CTG_KERNEL_CHECK(ctx);
-    const uint32_t ntiles = (nb + kScanTile - 1) / kScanTile;
-    if (ntiles > 1023) return fail(ctx, CTG_ERR_INVALID, "msm: too many buckets for the scan (c too large)");
-    msm_scan_tile_sum_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, nb, ws.tile_sums);
-    CTG_KERNEL_CHECK(ctx);
-    msm_scan_tiles_kernel<F><<<1, 1024, 0, st>>>(ws.tile_sums, ntiles);
-    CTG_KERNEL_CHECK(ctx);
-    msm_scan_apply_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, ws.cursor, nb, ws.tile_sums, ntiles);
-    CTG_KERNEL_CHECK(ctx);
-    msm_scatter_kernel<F><<<dig_blocks, 256, 0, st>>>(d_scalars, n, cstride, mont ? 1 : 0, plan, ws.cursor, ws.entries);
-    CTG_KERNEL_CHECK(ctx);
+    const uint32_t* starts = ws.counts;      // exclusive bucket offsets, [nb + 1]
+    const uint32_t* entries = ws.entries;
+    if (sorted) {
+      starts = sorted->counts;
+      entries = sorted->entries;
+    } else {
+      CTG_CUDA(ctx, cudaMemsetAsync(ws.counts, 0, (size_t)(nb + 1) * sizeof(uint32_t), st));
+      const int dig_x = (int)std::min<uint64_t>((n + 255) / 256, std::max<uint64_t>(1, (uint64_t)ctx->sm_count * 8 / batch));
+      const dim3 dig_grid(dig_x, batch);
+      msm_count_kernel<F><<<dig_grid, 256, 0, st>>>(d_scalars, n, vec_stride, mont ? 1 : 0, plan, ws.counts);
+      CTG_KERNEL_CHECK(ctx);
+      const uint32_t ntiles = (nb + kScanTile - 1) / kScanTile;
+      msm_scan_tile_sum_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, nb, ws.tile_sums);
+      CTG_KERNEL_CHECK(ctx);
+      msm_scan_tiles_kernel<F><<<1, 1024, 0, st>>>(ws.tile_sums, ntiles);
+      CTG_KERNEL_CHECK(ctx);
+      msm_scan_apply_kernel<F><<<ntiles, 256, 0, st>>>(ws.counts, ws.cursor, nb, ws.tile_sums, ntiles);
+      CTG_KERNEL_CHECK(ctx);
+      msm_scatter_kernel<F><<<dig_grid, 256, 0, st>>>(d_scalars, n, vec_stride, cstride, mont ? 1 : 0, plan, ws.cursor, ws.entries);
+      CTG_KERNEL_CHECK(ctx);
+      CTG_CUDA(ctx, cudaEventRecord(ws.ev_sorted, st));
+    }
     if (timed) CTG_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
 
     CTG_CUDA(ctx, cudaMemsetAsync(ws.buckets, 0, (size_t)nb * sizeof(XYZZ<F>), st));
     // 4a. batched-affine tree levels: level l reads level l-1 (level 1 the bases through the entry list)
-    const uint32_t* cur_starts = ws.counts;
+    const uint32_t* cur_starts = starts;
     const Affine<F>* cur_pts = nullptr;
     for (int l = 1; l <= ba_levels; l++) {
       uint32_t* out_starts = ws.ba_starts[(l - 1) & 1];
@@ -591,18 +615,18 @@ template <class F> struct MsmHost {
       ba_scan_launch<F>(st, cur_starts, out_starts, nb, ws.tile_sums);
       ctx->launches += 2;
       CTG_KERNEL_CHECK(ctx);
-      ba_level_launch<F>(ba_blocks, st, l == 1, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, cur_pts, cur_starts, out_starts, nb, out_pts);
+      ba_level_launch<F>(ba_blocks, st, l == 1, reinterpret_cast<const Affine<F>*>(bases.pts), entries, cur_pts, cur_starts, out_starts, nb, out_pts);
       CTG_KERNEL_CHECK(ctx);
       cur_starts = out_starts;
       cur_pts = out_pts;
     }
     // 4b. XYZZ accumulation of what is left
-    uint64_t want_threads = ((((uint64_t)n * plan.nwin) >> ba_levels) + 15) / 16;
+    uint64_t want_threads = ((((uint64_t)n * plan.nwin * batch) >> ba_levels) + 15) / 16;
     int blocks = (int)std::min<uint64_t>((want_threads + 127) / 128, (uint64_t)max_blocks);
     if (blocks < 1) blocks = 1;
     const uint32_t nslots = (uint32_t)blocks * 128 * 2;
     if (ba_levels > 0) accumulate_launch<F>(blocks, st, true, cur_pts, nullptr, cur_starts, nb, buckets, part_pt, ws.part_gb);
-    else accumulate_launch<F>(blocks, st, false, reinterpret_cast<const Affine<F>*>(bases.pts), ws.entries, ws.counts, nb, buckets, part_pt, ws.part_gb);
+    else accumulate_launch<F>(blocks, st, false, reinterpret_cast<const Affine<F>*>(bases.pts), entries, starts, nb, buckets, part_pt, ws.part_gb);
     CTG_KERNEL_CHECK(ctx);
     msm_fixup_short_kernel<F><<<(nslots + 127) / 128, 128, 0, st>>>(part_pt, ws.part_gb, nslots, buckets);
     CTG_KERNEL_CHECK(ctx);
@@ -612,7 +636,7 @@ template <class F> struct MsmHost {
 
     // bucket reduction (see section 6)
     {
-      const int nsets = plan.nsets;
+      const int nsets = plan.nsets * (int)batch;   // every vector of a batch has its own group of plan.nsets bucket sets
       XYZZ<F>* pool = chunk;   // bump allocator over the reduction scratch, in points
       size_t used = 0;
       auto take = [&](size_t pts) { XYZZ<F>* p = pool + used; used += pts * (size_t)nsets; return p; };
@@ -675,11 +699,11 @@ template <class F> struct MsmHost {
         CTG_KERNEL_CHECK(ctx);
         trees.swap(next);
       }
-      XYZZ<F>* set_out = nsets == 1 ? d_out : take(1);
+      XYZZ<F>* set_out = plan.nsets == 1 ? d_out : take(1);
       msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
       CTG_KERNEL_CHECK(ctx);
-      if (nsets > 1) {
-        msm_horner_kernel<F><<<1, 32, 0, st>>>(set_out, nsets, plan.c, d_out);
+      if (plan.nsets > 1) {
+        msm_horner_kernel<F><<<(batch + 31) / 32, 32, 0, st>>>(set_out, plan.nsets, plan.c, d_out, batch);
         CTG_KERNEL_CHECK(ctx);
       }
     }

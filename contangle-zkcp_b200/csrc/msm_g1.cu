@@ -40,8 +40,8 @@ MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t poin
 }
 
 int32_t msm_g1_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont, G1XYZZ* d_out,
-                   cudaStream_t st, float* stage_ms) {
-  return MsmHost<Fq>::run(ctx, ws, bases, d_scalars, n, scalars_mont, d_out, st, stage_ms);
+                   cudaStream_t st, float* stage_ms, uint32_t batch, uint64_t vec_stride, const MsmWorkspace* sorted) {
+  return MsmHost<Fq>::run(ctx, ws, bases, d_scalars, n, scalars_mont, d_out, st, stage_ms, batch, vec_stride, sorted);
 }
 int32_t g1_precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st) { return MsmHost<Fq>::precompute(ctx, b, st); }
 int32_t g1_to_affine_dev(ctg_ctx* ctx, const G1XYZZ* d_in, G1Affine* d_out, int count, cudaStream_t st) {
@@ -61,6 +61,7 @@ void msm_ws_free(MsmWorkspace& ws) {
                   ws.ba_pts[0], ws.ba_pts[1], ws.ba_starts[0], ws.ba_starts[1]};
   for (void* p : ptrs)
     if (p) cudaFree(p);
+  if (ws.ev_sorted) cudaEventDestroy(ws.ev_sorted);
   ws = MsmWorkspace();
 }
 

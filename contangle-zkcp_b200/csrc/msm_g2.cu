@@ -6,8 +6,8 @@
 namespace ctg {
 
 int32_t msm_g2_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont, G2XYZZ* d_out,
-                   cudaStream_t st, float* stage_ms) {
-  return MsmHost<Fq2>::run(ctx, ws, bases, d_scalars, n, scalars_mont, d_out, st, stage_ms);
+                   cudaStream_t st, float* stage_ms, uint32_t batch, uint64_t vec_stride, const MsmWorkspace* sorted) {
+  return MsmHost<Fq2>::run(ctx, ws, bases, d_scalars, n, scalars_mont, d_out, st, stage_ms, batch, vec_stride, sorted);
 }
 int32_t g2_precompute(ctg_ctx* ctx, Bases& b, cudaStream_t st) { return MsmHost<Fq2>::precompute(ctx, b, st); }
 int32_t g2_to_affine_dev(ctg_ctx* ctx, const G2XYZZ* d_in, G2Affine* d_out, int count, cudaStream_t st) {

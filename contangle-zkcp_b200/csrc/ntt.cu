@@ -76,8 +76,10 @@ __device__ __forceinline__ uint64_t bitrev_idx(uint64_t a, int log_n) {
   return log_n == 0 ? 0 : (uint64_t)(__brev((uint32_t)a) >> (32 - log_n));
 }
 
+// blockIdx.y = index of the transform in a batch of equal-size transforms stored back to back
 __global__ void __launch_bounds__(kThreads) ntt_pass_kernel(Fr* __restrict__ data, NttPass p) {
   extern __shared__ uint4 smem[];
+  data += (uint64_t)blockIdx.y << p.log_n;
   const int tile = 1 << p.log_tile;
   uint4* lo = smem;
   uint4* hi = smem + tile;
@@ -271,11 +273,9 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
   CTG_TRY(fill_pow_table(ctx, d.gpow, n, g, Fr::one(), st));
   CTG_TRY(fill_pow_table(ctx, d.gpow_n, n, g, d.n_inv, st));
   CTG_TRY(fill_pow_table(ctx, d.gipow_n, n, gi, d.n_inv, st));
-  static bool attr_set = false;
-  if (!attr_set) {
+  // a per-device attribute: once per context, not once per process (a multi-device context has one context per GPU)
+  if (ctx->domains.empty())
     CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32));
-    attr_set = true;
-  }
   CTG_CUDA(ctx, cudaStreamSynchronize(st));  // other streams (prover lanes) may use the tables next
   ctx->domains[log_n] = d;
   *out = &ctx->domains[log_n];
@@ -304,11 +304,12 @@ struct Fuse {
 };
 
 // Runs all passes of one transform.  dit = 0: natural -> bit-reversed; dit = 1: the reverse.
-static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit, const Fuse& f, cudaStream_t st) {
+static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit, const Fuse& f, cudaStream_t st, uint32_t batch = 1) {
   std::vector<PassGeom> plan = plan_passes(log_n);
   if (dit) std::reverse(plan.begin(), plan.end());
   const uint64_t n = 1ull << log_n;
   if (plan.empty()) {  // n == 1: only the scale factors act
+    if (batch != 1) return fail(ctx, CTG_ERR_INVALID, "ntt: batched transforms need n >= 2");
     if (f.pre_tab) { scale_table_kernel<<<1, 32, 0, st>>>(d, 1, f.pre_tab, Fr::one(), 0); CTG_KERNEL_CHECK(ctx); }
     if (f.post_tab) { scale_table_kernel<<<1, 32, 0, st>>>(d, 1, f.post_tab, Fr::one(), 0); CTG_KERNEL_CHECK(ctx); }
     if (f.post_const) { scale_table_kernel<<<1, 32, 0, st>>>(d, 1, nullptr, f.post_c, 1); CTG_KERNEL_CHECK(ctx); }
@@ -331,7 +332,7 @@ static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit,
     p.post_c = f.post_c;
     unsigned blocks = (unsigned)(n >> p.log_tile);
     size_t smem = ((size_t)1 << p.log_tile) * 32;
-    ntt_pass_kernel<<<blocks, kThreads, smem, st>>>(d, p);
+    ntt_pass_kernel<<<dim3(blocks, batch), kThreads, smem, st>>>(d, p);
     CTG_KERNEL_CHECK(ctx);
   }
   return CTG_OK;
@@ -358,24 +359,24 @@ int32_t ntt_run(ctg_ctx* ctx, Fr* d, int log_n, int inverse, int coset, cudaStre
   return CTG_OK;
 }
 
-int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d, int log_n, cudaStream_t st) {
+int32_t ntt_ifft_then_coset_fft(ctg_ctx* ctx, Fr* d, int log_n, cudaStream_t st, uint32_t batch) {
   NttDomain* dom;
   CTG_TRY(ntt_get_domain(ctx, log_n, &dom));
   Fuse f;
   f.post_tab = dom->gpow_n;  // (1/n) * g^i, i = natural index of the bit-reversed slot
   f.post_bitrev = 1;
-  CTG_TRY(run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st));
+  CTG_TRY(run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st, batch));
   Fuse none;
-  return run_passes(ctx, d, log_n, dom->tw_fwd, 1, none, st);
+  return run_passes(ctx, d, log_n, dom->tw_fwd, 1, none, st, batch);
 }
 
-int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d, int log_n, cudaStream_t st) {
+int32_t ntt_coset_ifft_bitrev(ctg_ctx* ctx, Fr* d, int log_n, cudaStream_t st, uint32_t batch) {
   NttDomain* dom;
   CTG_TRY(ntt_get_domain(ctx, log_n, &dom));
   Fuse f;
   f.post_tab = dom->gipow_n;
   f.post_bitrev = 1;
-  return run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st);
+  return run_passes(ctx, d, log_n, dom->tw_inv, 0, f, st, batch);
 }
 
 }  // namespace ctg

@@ -15,35 +15,22 @@
 //            overwritten by -(r s)                                              ->  H - rs delta
 // so r*delta, s*delta, alpha, beta and -rs*delta ride along in the MSMs (z[0] = 1 already
 // selects query[0]).  Only s*A and r*B1 remain as scalar multiplications of results.
-#include "ctg_internal.h"
+#include <algorithm>
+#include <cstdlib>
 
-struct ctg_pk {
-  uint64_t m, ni, nw, n;
-  int log_n;
-  // point-range shard (multi-GPU): this key holds positions [lo, lo + cnt) of each extended query
-  int shard_index = 0, shard_count = 1;
-  uint64_t ext_lo = 0, ext_cnt = 0;  // of a_ext / b1_ext / b2_ext (m + 3 positions)
-  uint64_t l_lo = 0, l_cnt = 0;      // of l (num_witness positions)
-  uint64_t h_lo = 0, h_cnt = 0;      // of h_ext (n positions, bit-reversed order)
-  ctg::Bases a_ext, b1_ext, b2_ext, l, h_ext;
-};
-struct ctg_r1cs {
-  uint64_t ni, nw, nc, n;
-  int log_n;
-  uint64_t* row_ptr[3];
-  uint32_t* col[3];
-  ctg::Fr* val[3];
-  uint64_t nnz[3];
-};
+#include "ctg_internal.h"
 
 namespace ctg {
 
 // ---- witness map kernels --------------------------------------------------------------------
 // out[i] = <M_i, z> for i < nc; for the A matrix rows nc..nc+ni copy z[j] (input consistency); else 0
+// blockIdx.y = proof of a batch: assignment z + y * z_stride, output out + y * n (0 strides for a single proof)
 __global__ void spmv_kernel(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col, const Fr* __restrict__ val,
-                            const Fr* __restrict__ z, Fr* __restrict__ out, uint64_t nc, uint64_t ni, uint64_t n, int is_a) {
+                            const Fr* __restrict__ z, Fr* __restrict__ out, uint64_t nc, uint64_t ni, uint64_t n, int is_a, uint64_t z_stride) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  z += (uint64_t)blockIdx.y * z_stride;
+  out += (uint64_t)blockIdx.y * n;
   Fr acc = Fr::zero();
   if (i < nc) {
     const uint64_t lo = row_ptr[i], hi = row_ptr[i + 1];
@@ -68,6 +55,20 @@ __global__ void set_tail_kernel(Fr* z_ext, uint64_t m, Fr r, Fr s) {
 }
 __global__ void set_h_tail_kernel(Fr* h, uint64_t n, Fr r, Fr s) {
   if (threadIdx.x == 0 && blockIdx.x == 0) h[n - 1] = (r * s).neg();
+}
+// batched forms: proof p of the batch has its assignment at z_ext + p * (m + 3), its h at h + p * n and (r, s) at rs[2p], rs[2p + 1]
+__global__ void set_tail_batch_kernel(Fr* z_ext, uint64_t m, const Fr* __restrict__ rs, uint32_t batch) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= batch) return;
+  Fr* t = z_ext + (uint64_t)p * (m + 3) + m;
+  t[0] = Fr::one();
+  t[1] = rs[2 * p];
+  t[2] = rs[2 * p + 1];
+}
+__global__ void set_h_tail_batch_kernel(Fr* h, uint64_t n, const Fr* __restrict__ rs, uint32_t batch) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= batch) return;
+  h[(uint64_t)p * n + (n - 1)] = (rs[2 * p] * rs[2 * p + 1]).neg();
 }
 __global__ void bitrev_gather_fr_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, int log_n) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -131,6 +132,39 @@ __global__ void __launch_bounds__(96) finalize_kernel(FinalizeIn in, ctg_proof* 
     } else if (warp == 1) {
       G1Affine aa = xyzz_to_affine(*in.a);
       *reinterpret_cast<G1Affine*>(&out->a) = aa;
+    }
+  }
+}
+
+// one block per proof of a batch: results laid out a[p], b1[p], l[p], h[p], b2[p]; (r, s) at rs[2p], rs[2p + 1]
+struct FinalizeBatchIn { const G1XYZZ *a, *b1, *l, *h; const G2XYZZ* b2; const Fr* rs; };
+__global__ void __launch_bounds__(96) finalize_batch_kernel(FinalizeBatchIn in, ctg_proof* out) {
+  __shared__ G1XYZZ sh[2];
+  const uint32_t p = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    if (warp == 0) {
+      Fr k = in.rs[2 * p + 1].from_mont();
+      sh[0] = xyzz_mul(in.a[p], k.v);
+    } else if (warp == 1) {
+      Fr k = in.rs[2 * p].from_mont();
+      sh[1] = xyzz_mul(in.b1[p], k.v);
+    } else {
+      G2Affine b = xyzz_to_affine(in.b2[p]);
+      *reinterpret_cast<G2Affine*>(&out[p].b) = b;
+    }
+  }
+  __syncthreads();
+  if (lane == 0) {
+    if (warp == 0) {
+      G1XYZZ c = xyzz_add(sh[0], sh[1]);
+      c = xyzz_add(c, in.l[p]);
+      c = xyzz_add(c, in.h[p]);
+      G1Affine ca = xyzz_to_affine(c);
+      *reinterpret_cast<G1Affine*>(&out[p].c) = ca;
+    } else if (warp == 1) {
+      G1Affine aa = xyzz_to_affine(in.a[p]);
+      *reinterpret_cast<G1Affine*>(&out[p].a) = aa;
     }
   }
 }
@@ -241,7 +275,7 @@ void pk_free(ctg_pk* pk) {
 int32_t r1cs_upload(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, const ctg_csr* const mats[3], ctg_r1cs** out) {
   if (ni == 0) return fail(ctx, CTG_ERR_INVALID, "r1cs_upload: num_instance includes the constant 1 and must be >= 1");
   ctg_r1cs* r = new ctg_r1cs();
-  memset(r, 0, sizeof(*r));
+  for (int k = 0; k < 3; k++) { r->row_ptr[k] = nullptr; r->col[k] = nullptr; r->val[k] = nullptr; r->nnz[k] = 0; }
   r->ni = ni; r->nw = nw; r->nc = nc;
   uint64_t n = 1; int log_n = 0;
   while (n < nc + ni) { n <<= 1; log_n++; }
@@ -286,14 +320,14 @@ void r1cs_free(ctg_r1cs* r) {
 // d_z: m (+3) Montgomery elements on the device.  d_abc: 3 * n scratch.  Leaves h (bit-reversed,
 // Montgomery) in d_abc[0..n).
 // chain k (0 = a, 1 = b, 2 = c): SpMV, then ifft + coset_fft fused -> coset evaluations in v (n elements, natural order)
-static int32_t witness_chain_dev(ctg_ctx* ctx, const ctg_r1cs* r, const Fr* d_z, Fr* v, int k, cudaStream_t st) {
+int32_t witness_chain_dev(ctg_ctx* ctx, const ctg_r1cs* r, const Fr* d_z, Fr* v, int k, cudaStream_t st) {
   const uint64_t n = r->n;
-  spmv_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(r->row_ptr[k], r->col[k], r->val[k], d_z, v, r->nc, r->ni, n, k == 0);
+  spmv_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(r->row_ptr[k], r->col[k], r->val[k], d_z, v, r->nc, r->ni, n, k == 0, 0);
   CTG_KERNEL_CHECK(ctx);
   return ntt_ifft_then_coset_fft(ctx, v, r->log_n, st);
 }
 // (a b - c) / Z on the coset, then coset_ifft: h (bit-reversed, Montgomery) in d_abc[0..n)
-static int32_t witness_finish_dev(ctg_ctx* ctx, const ctg_r1cs* r, Fr* d_abc, cudaStream_t st) {
+int32_t witness_finish_dev(ctg_ctx* ctx, const ctg_r1cs* r, Fr* d_abc, cudaStream_t st) {
   const uint64_t n = r->n;
   NttDomain* dom;
   CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
@@ -325,7 +359,7 @@ int32_t witness_map_host(ctg_ctx* ctx, const ctg_r1cs* r, const ctg_fr* z, ctg_f
 }
 
 // ---- host: prover lanes -----------------------------------------------------------------------
-static int32_t lane_init(ctg_ctx* ctx, int idx) {
+int32_t lane_init(ctg_ctx* ctx, int idx) {
   ProveLane& L = ctx->lanes[idx];
   if (L.ready) { if (idx == 0) L.st[0] = ctx->stream; return CTG_OK; }
   for (int i = 0; i < 5; i++) {
@@ -365,7 +399,7 @@ void lanes_destroy(ctg_ctx* ctx) {
   if (ctx->pinned_proofs) cudaFreeHost(ctx->pinned_proofs);
   ctx->pinned_proofs = nullptr;
 }
-static int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
+int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
   if (bytes <= L.scratch_bytes) return CTG_OK;
   if (L.scratch) {
     for (int i = 0; i < 5; i++) CTG_CUDA(ctx, cudaStreamSynchronize(L.st[i]));
@@ -379,6 +413,28 @@ static int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
   return CTG_OK;
 }
 
+// two tables whose MSMs over the same scalars produce the same sorted entry list
+static bool same_plan(const Bases& a, const Bases& b) {
+  return a.plan.c == b.plan.c && a.plan.nwin == b.plan.nwin && a.plan.copies == b.plan.copies && a.plan.nsets == b.plan.nsets &&
+         a.n == b.n && (a.stride ? a.stride : a.n) == (b.stride ? b.stride : b.n);
+}
+
+// scratch of a lane: z_ext (m+3) | a,b,c (3n, unless the caller owns that buffer) | results: 4 G1 XYZZ + 1 G2 XYZZ | proof
+int32_t lane_bufs(ctg_ctx* ctx, ProveLane& L, uint64_t m, uint64_t n, Fr* d_abc_ext, LaneBufs* out) {
+  const size_t fr_elems = m + 3 + (d_abc_ext ? 0 : 3 * n);
+  const size_t bytes = fr_elems * sizeof(Fr) + 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ) + sizeof(ctg_proof) + 256;
+  CTG_TRY(lane_scratch(ctx, L, bytes));
+  out->d_z = (Fr*)L.scratch;
+  Fr* after = out->d_z + (m + 3);
+  out->d_abc = d_abc_ext ? d_abc_ext : after;
+  char* tail = (char*)(d_abc_ext ? after : after + 3 * n);
+  tail = (char*)(((uintptr_t)tail + 63) & ~(uintptr_t)63);
+  out->d_g1 = (G1XYZZ*)tail;
+  out->d_g2 = (G2XYZZ*)(out->d_g1 + 4);
+  out->d_proof = (ctg_proof*)(out->d_g2 + 1);
+  return CTG_OK;
+}
+
 // Enqueues one proof (or one shard's partial sums) on a lane; no host synchronisation.
 //   d_proof_out != nullptr : full proof (shard_count must be 1), written to device memory d_proof_out
 //   d_partials_out != nullptr : this shard's partial sums [A, B1, L, H] (4 G1 XYZZ) then B2 (G2 XYZZ), 1152 bytes
@@ -389,18 +445,13 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   CTG_TRY(lane_init(ctx, lane_idx));
   ProveLane& L = ctx->lanes[lane_idx];
   const uint64_t n = r->n, m = pk->m;
-  // scratch: z_ext (m+3) | a,b,c (3n) | results: 4 G1 XYZZ + 1 G2 XYZZ | proof
-  const size_t fr_elems = m + 3 + 3 * n;
-  const size_t bytes = fr_elems * sizeof(Fr) + 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ) + sizeof(ctg_proof) + 256;
-  CTG_TRY(lane_scratch(ctx, L, bytes));
-  Fr* d_z = (Fr*)L.scratch;
-  Fr* d_abc = d_z + (m + 3);
-  char* tail = (char*)(d_abc + 3 * n);
-  if (d_abc_ext) d_abc = d_abc_ext;
-  tail = (char*)(((uintptr_t)tail + 63) & ~(uintptr_t)63);
-  G1XYZZ* d_g1 = (G1XYZZ*)tail;           // [0]=A [1]=B1 [2]=L [3]=H
-  G2XYZZ* d_g2 = (G2XYZZ*)(d_g1 + 4);
-  ctg_proof* d_proof = (ctg_proof*)(d_g2 + 1);
+  LaneBufs B;
+  CTG_TRY(lane_bufs(ctx, L, m, n, d_abc_ext, &B));
+  Fr* d_z = B.d_z;
+  Fr* d_abc = B.d_abc;
+  G1XYZZ* d_g1 = B.d_g1;           // [0]=A [1]=B1 [2]=L [3]=H
+  G2XYZZ* d_g2 = B.d_g2;
+  ctg_proof* d_proof = B.d_proof;
   cudaStream_t s0 = L.st[0];
   cudaStream_t sw = L.st_hi;   // witness map + H MSM
   int ne = 0;
@@ -436,14 +487,20 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
     cudaStream_t st = L.st[j.stream];
     CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
     mark(st);                                                                 // 2,4,6,8
-    if (j.g1_slot >= 0) CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr));
-    else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
+    if (j.g1_slot >= 0) {
+      // A and B1 multiply the same scalars under the same plan: B1 reuses A's sorted entry list (one digit sort fewer per proof)
+      const MsmWorkspace* sorted = nullptr;
+      if (j.stream == 3 && j.cnt > 0 && same_plan(pk->a_ext, pk->b1_ext)) { sorted = &L.ws[2]; CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ws[2].ev_sorted, 0)); }
+      CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr, 1, 0, sorted));
+    } else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
     mark(st);                                                                 // 3,5,7,9
     CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
   }
   // witness map on the lane's main stream: the coset evaluations of a, b, c (the chains this rank owns) ...
-  NttDomain* dom;
-  CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
+  if (phase != 1 || chain_mask != 0) {   // tables are built (and synchronised) before any chain is enqueued
+    NttDomain* dom;
+    CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
+  }
   CTG_CUDA(ctx, cudaStreamWaitEvent(sw, L.ev_zfull, 0));
   for (int k = 0; k < 3; k++)
     if (chain_mask & (1u << k)) CTG_TRY(witness_chain_dev(ctx, r, d_z, d_abc + (uint64_t)k * n, k, sw));
@@ -508,8 +565,92 @@ int32_t prove(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z
   return CTG_OK;
 }
 
-// Independent proofs pipelined over the lanes: while one proof sits in its latency-bound tails (bucket reduction,
-// inversions) the next one's kernels fill the SMs.  Results are staged in pinned memory.
+// ---- batched prover: many proofs of ONE circuit under ONE key (the reference's production shape: a key-encryption proof per
+// buyer request, lib/src/seller.rs:136-159, and per-chunk proofs "computed in parallel", docs/protocol.md:56) ------------------
+// A chunk of up to kBatchMax proofs goes through the pipeline TOGETHER: one SpMV launch per matrix and one launch per NTT pass
+// for all of them (blockIdx.y = proof), and each of the five MSMs is ONE digit sort + ONE accumulate pass + ONE reduction over
+// the chunk's scalar vectors against the shared base table (bucket-set group = proof; msm.cuh run(batch)).  The latency-bound
+// tails that dominate a lone small proof (bucket reduction, inversions) become wide, throughput-bound launches, and the launch
+// count per proof drops from ~100 to ~170 / chunk.  A and B1 share one digit sort (same scalars, same plan).
+static constexpr uint32_t kBatchMax = 256;
+static uint32_t batch_chunk(const ctg_pk* pk, const ctg_r1cs* r, uint32_t n_proofs) {
+  uint64_t c = std::min<uint64_t>(n_proofs, kBatchMax);
+  for (const Bases* b : {&pk->a_ext, &pk->b1_ext, &pk->b2_ext, &pk->l, &pk->h_ext}) {
+    if (b->n == 0) continue;
+    const uint64_t per_nb = (uint64_t)b->plan.nsets * b->plan.nbuckets_per_set, per_ne = b->n * (uint64_t)b->plan.nwin;
+    c = std::min<uint64_t>(c, (1023ull * 2048) / per_nb);          // the bucket-offset scan handles 1023 tiles of 2048 buckets
+    c = std::min<uint64_t>(c, ((1ull << 28) - 1) / per_ne);        // <= 2^28 sorted entries (1 GiB) per MSM
+  }
+  (void)r;
+  return (uint32_t)std::max<uint64_t>(c, 1);
+}
+
+static int32_t prove_batch_fused(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t B, const ctg_fr* z_batch, const ctg_fr* rs_batch, ctg_proof* staged) {
+  CTG_TRY(lane_init(ctx, 0));
+  ProveLane& L = ctx->lanes[0];
+  const uint64_t n = r->n, m = pk->m, zs = m + 3;
+  // scratch: z_ext [B][m+3] | rs [B][2] | a, b, c [3][B][n] | results G1 [4][B], G2 [B] | proofs [B]
+  const size_t fr_elems = (size_t)B * zs + 2 * (size_t)B + 3 * (size_t)B * n;
+  const size_t bytes = fr_elems * sizeof(Fr) + (size_t)B * (4 * sizeof(G1XYZZ) + sizeof(G2XYZZ) + sizeof(ctg_proof)) + 512;
+  CTG_TRY(lane_scratch(ctx, L, bytes));
+  Fr* d_z = (Fr*)L.scratch;
+  Fr* d_rs = d_z + (size_t)B * zs;
+  Fr* d_abc = d_rs + 2 * (size_t)B;
+  char* tail = (char*)(d_abc + 3 * (size_t)B * n);
+  tail = (char*)(((uintptr_t)tail + 63) & ~(uintptr_t)63);
+  G1XYZZ* d_g1 = (G1XYZZ*)tail;                 // [0..B) = A, [B..2B) = B1, [2B..3B) = L, [3B..4B) = H
+  G2XYZZ* d_g2 = (G2XYZZ*)(d_g1 + 4 * (size_t)B);
+  ctg_proof* d_proof = (ctg_proof*)(d_g2 + B);
+  cudaStream_t s0 = L.st[0], sw = L.st_hi;
+  NttDomain* dom;
+  CTG_TRY(ntt_get_domain(ctx, r->log_n, &dom));
+  CTG_CUDA(ctx, cudaMemcpy2DAsync(d_z, zs * sizeof(Fr), z_batch, m * sizeof(Fr), m * sizeof(Fr), B, cudaMemcpyHostToDevice, s0));
+  CTG_CUDA(ctx, cudaMemcpyAsync(d_rs, rs_batch, 2 * (size_t)B * sizeof(Fr), cudaMemcpyHostToDevice, s0));
+  set_tail_batch_kernel<<<(B + 127) / 128, 128, 0, s0>>>(d_z, m, d_rs, B);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_z, s0));
+  struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
+  const Job jobs[4] = {{1, &pk->l, d_z + pk->ni, pk->l_cnt, 2}, {2, &pk->a_ext, d_z, pk->ext_cnt, 0}, {3, &pk->b1_ext, d_z, pk->ext_cnt, 1}, {4, &pk->b2_ext, d_z, pk->ext_cnt, -1}};
+  const bool share = same_plan(pk->a_ext, pk->b1_ext) && pk->ext_cnt > 0;
+  for (const Job& j : jobs) {
+    cudaStream_t st = L.st[j.stream];
+    CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
+    if (j.g1_slot >= 0) {
+      const MsmWorkspace* sorted = nullptr;
+      if (j.stream == 3 && share) { sorted = &L.ws[2]; CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ws[2].ev_sorted, 0)); }
+      CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + (size_t)j.g1_slot * B, st, nullptr, B, zs, sorted));
+    } else {
+      CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr, B, zs));
+    }
+    CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
+  }
+  // witness map of the whole chunk on the high-priority stream: chains k = a, b, c are stored [k][proof][n]
+  CTG_CUDA(ctx, cudaStreamWaitEvent(sw, L.ev_z, 0));
+  for (int k = 0; k < 3; k++) {
+    spmv_kernel<<<dim3((unsigned)((n + 127) / 128), B), 128, 0, sw>>>(r->row_ptr[k], r->col[k], r->val[k], d_z, d_abc + (size_t)k * B * n, r->nc, r->ni, n, k == 0, zs);
+    CTG_KERNEL_CHECK(ctx);
+  }
+  if (r->log_n == 0) return fail(ctx, CTG_ERR_STATE, "prove_batch: internal: the fused path needs a domain of at least 2");
+  CTG_TRY(ntt_ifft_then_coset_fft(ctx, d_abc, r->log_n, sw, 3 * B));
+  const uint64_t tot = (uint64_t)B * n;
+  pointwise_kernel<<<(unsigned)((tot + 127) / 128), 128, 0, sw>>>(d_abc, d_abc + tot, d_abc + 2 * tot, dom->zinv, tot);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_TRY(ntt_coset_ifft_bitrev(ctx, d_abc, r->log_n, sw, B));
+  set_h_tail_batch_kernel<<<(B + 127) / 128, 128, 0, sw>>>(d_abc, n, d_rs, B);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_TRY(msm_g1_run(ctx, L.ws[0], pk->h_ext, (const uint32_t*)d_abc, pk->h_cnt, true, d_g1 + 3 * (size_t)B, sw, nullptr, B, n));
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_wm, sw));
+  CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_wm, 0));
+  for (int i = 1; i < 5; i++) CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_done[i], 0));
+  FinalizeBatchIn fin{d_g1, d_g1 + B, d_g1 + 2 * (size_t)B, d_g1 + 3 * (size_t)B, d_g2, d_rs};
+  finalize_batch_kernel<<<B, 96, 0, s0>>>(fin, d_proof);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_CUDA(ctx, cudaMemcpyAsync(staged, d_proof, (size_t)B * sizeof(ctg_proof), cudaMemcpyDeviceToHost, s0));
+  return CTG_OK;
+}
+
+// Small circuits (domain <= 2^17): chunks through the fused pipeline above.  Large ones saturate the GPU proof by proof; they
+// are pipelined over two stream sets so that one proof's latency-bound tails overlap the next one's kernels.
 int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t n_proofs, const ctg_fr* z_batch, const ctg_fr* rs_batch, ctg_proof* out) {
   CTG_TRY(check_prove_args(ctx, pk, r));
   if (pk->shard_count != 1) return fail(ctx, CTG_ERR_STATE, "prove_batch: the key is a shard");
@@ -522,9 +663,20 @@ int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t 
     ctx->pinned_proofs_bytes = need;
   }
   ctg_proof* staged = (ctg_proof*)ctx->pinned_proofs;
-  // small circuits are latency-bound: use every lane; large ones saturate the GPU alone and only need two
-  const int lanes = r->n <= (1u << 18) ? kMaxLanes : 2;
   const uint64_t m = pk->m;
+  static int fused_max_log = -1;
+  if (fused_max_log < 0) { const char* e = getenv("CTG_BATCH_FUSED_MAX_LOG_N"); fused_max_log = e ? atoi(e) : 17; }
+  if (r->log_n >= 1 && r->log_n <= fused_max_log && n_proofs > 1) {
+    const uint32_t chunk = batch_chunk(pk, r, n_proofs);
+    for (uint32_t lo = 0; lo < n_proofs; lo += chunk) {
+      const uint32_t cnt = std::min(chunk, n_proofs - lo);
+      CTG_TRY(prove_batch_fused(ctx, pk, r, cnt, z_batch + (size_t)lo * m, rs_batch + 2 * (size_t)lo, staged + lo));
+    }
+    CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));
+    memcpy(out, staged, need);
+    return CTG_OK;
+  }
+  const int lanes = r->n <= (1u << 18) ? kMaxLanes : 2;
   for (uint32_t i = 0; i < n_proofs; i++) {
     Fr r_m, s_m;
     memcpy(&r_m, rs_batch + 2 * (size_t)i, sizeof(Fr));
@@ -605,6 +757,93 @@ int32_t prove_combine(ctg_ctx* ctx, const void* host_partials, uint32_t k, const
   return CTG_OK;
 }
 
-uint64_t pk_num_vars(const ctg_pk* pk) { return pk->m; }
+uint64_t pk_num_vars(const ctg_pk* pk) { return pk->parts.empty() ? pk->m : pk->parts[0]->m; }
+
+// ---- multi-device proof: one process, one worker thread per device, peer copies over NVLink ---------------------------
+// Phases (multi.cu runs A on every device, then B on device 0, then C on every device, then D on device 0; the host only
+// orders the ENQUEUE of the phases -- cudaStreamWaitEvent needs its event recorded first -- and synchronises once at the end):
+//   A  upload the part of z this device reads, start its A / B1 / B2 / L MSMs, compute the witness-map chains it owns
+//   B  device 0 pulls the chains it does not own from their owners (n * 32 B each), runs (a b - c)/Z and the coset_ifft ONCE
+//   C  every device pulls ITS slice of h (n / N * 32 B) from device 0, runs its H MSM, and pushes 1152 B of partial sums to device 0
+//   D  device 0 sums the partials and assembles (A, B, C)
+// Bytes over NVLink per proof: 2-3 chains + one vector of h in slices, instead of broadcasting three chains to every device.
+int32_t prove_group_a(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const Fr& r_m, const Fr& s_m, uint32_t chain_mask, Fr* d_abc,
+                      cudaEvent_t ev_done) {
+  CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, nullptr, nullptr, false, 1, chain_mask, d_abc));
+  CTG_CUDA(ctx, cudaEventRecord(ev_done, ctx->lanes[0].st[0]));   // s0 is ordered after the chains (prove_enqueue phase 1)
+  return CTG_OK;
+}
+int32_t prove_group_b(Group* g, const ctg_r1cs* r0, const Fr& r_m, const Fr& s_m) {
+  ctg_ctx* ctx = g->ctx[0];
+  ProveLane& L = ctx->lanes[0];
+  cudaStream_t s0 = L.st[0], sw = L.st_hi;
+  const uint64_t n = r0->n;
+  for (int k = 0; k < 3; k++) {
+    const int o = g->chain_owner[k];
+    if (o == 0) continue;
+    CTG_CUDA(ctx, cudaStreamWaitEvent(s0, g->ev_a[o], 0));
+    CTG_CUDA(ctx, cudaMemcpyPeerAsync(g->d_abc[0] + (uint64_t)k * n, g->ctx[0]->device, g->d_abc[o] + (uint64_t)k * n, g->ctx[o]->device, n * sizeof(Fr), s0));
+  }
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_zfull, s0));
+  CTG_CUDA(ctx, cudaStreamWaitEvent(sw, L.ev_zfull, 0));
+  CTG_TRY(witness_finish_dev(ctx, r0, g->d_abc[0], sw));
+  set_h_tail_kernel<<<1, 32, 0, sw>>>(g->d_abc[0], n, r_m, s_m);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_CUDA(ctx, cudaEventRecord(g->ev_h, sw));
+  return CTG_OK;
+}
+int32_t prove_group_c(Group* g, int d, const ctg_pk* pk, const ctg_r1cs* r) {
+  ctg_ctx* ctx = g->ctx[d];
+  ProveLane& L = ctx->lanes[0];
+  cudaStream_t s0 = L.st[0], sw = L.st_hi;
+  LaneBufs B;
+  CTG_TRY(lane_bufs(ctx, L, pk->m, r->n, d == 0 ? g->d_abc[0] : g->d_hslice[d], &B));
+  const Fr* h_scalars = g->d_abc[0] + pk->h_lo;
+  if (d != 0) {
+    CTG_CUDA(ctx, cudaStreamWaitEvent(sw, g->ev_h, 0));
+    if (pk->h_cnt)
+      CTG_CUDA(ctx, cudaMemcpyPeerAsync(g->d_hslice[d], ctx->device, g->d_abc[0] + pk->h_lo, g->ctx[0]->device, pk->h_cnt * sizeof(Fr), sw));
+    h_scalars = g->d_hslice[d];
+  }
+  CTG_TRY(msm_g1_run(ctx, L.ws[0], pk->h_ext, (const uint32_t*)h_scalars, pk->h_cnt, true, B.d_g1 + 3, sw, nullptr));
+  CTG_CUDA(ctx, cudaEventRecord(L.ev_wm, sw));
+  CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_wm, 0));
+  for (int i = 1; i < 5; i++) CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_done[i], 0));
+  CTG_CUDA(ctx, cudaMemcpyPeerAsync((char*)g->d_parts0 + (size_t)d * kPartialBytes, g->ctx[0]->device, B.d_g1, ctx->device, kPartialBytes, s0));
+  CTG_CUDA(ctx, cudaEventRecord(g->ev_part[d], s0));
+  return CTG_OK;
+}
+// the k-th shard's partials sit at parts + k * 1152: [A, B1, L, H] G1 XYZZ then B2 G2 XYZZ
+__global__ void __launch_bounds__(160) combine_partials_packed_kernel(const char* parts, uint32_t k, G1XYZZ* out_g1, G2XYZZ* out_g2) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane != 0) return;
+  if (warp < 4) {
+    G1XYZZ acc = reinterpret_cast<const G1XYZZ*>(parts)[warp];
+    for (uint32_t i = 1; i < k; i++) acc = xyzz_add(acc, reinterpret_cast<const G1XYZZ*>(parts + (size_t)i * kPartialBytes)[warp]);
+    out_g1[warp] = acc;
+  } else {
+    G2XYZZ acc = *reinterpret_cast<const G2XYZZ*>(parts + 4 * sizeof(G1XYZZ));
+    for (uint32_t i = 1; i < k; i++) acc = xyzz_add(acc, *reinterpret_cast<const G2XYZZ*>(parts + (size_t)i * kPartialBytes + 4 * sizeof(G1XYZZ)));
+    *out_g2 = acc;
+  }
+}
+int32_t prove_group_d(Group* g, const Fr& r_m, const Fr& s_m, ctg_proof* out) {
+  ctg_ctx* ctx = g->ctx[0];
+  cudaStream_t s0 = ctx->lanes[0].st[0];
+  for (int d = 1; d < g->n; d++) CTG_CUDA(ctx, cudaStreamWaitEvent(s0, g->ev_part[d], 0));
+  char* base = (char*)g->d_parts0;
+  G1XYZZ* d_s1 = (G1XYZZ*)(base + (size_t)g->n * kPartialBytes);
+  G2XYZZ* d_s2 = (G2XYZZ*)(d_s1 + 4);
+  ctg_proof* d_proof = (ctg_proof*)(d_s2 + 1);
+  combine_partials_packed_kernel<<<1, 160, 0, s0>>>(base, (uint32_t)g->n, d_s1, d_s2);
+  CTG_KERNEL_CHECK(ctx);
+  FinalizeIn fin{d_s1 + 0, d_s1 + 1, d_s1 + 2, d_s1 + 3, d_s2, r_m, s_m};
+  finalize_kernel<<<1, 96, 0, s0>>>(fin, d_proof);
+  CTG_KERNEL_CHECK(ctx);
+  CTG_CUDA(ctx, cudaMemcpyAsync(g->h_proof, d_proof, sizeof(ctg_proof), cudaMemcpyDeviceToHost, s0));
+  CTG_CUDA(ctx, cudaStreamSynchronize(s0));
+  memcpy(out, g->h_proof, sizeof(ctg_proof));
+  return CTG_OK;
+}
 
 }  // namespace ctg

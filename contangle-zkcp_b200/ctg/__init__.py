@@ -25,7 +25,7 @@ OP_MUL, OP_ADD, OP_SUB, OP_INV = 0, 1, 2, 3
 
 # every symbol include/ctg_groth16.h declares (checked by tests/test_abi_cpu.py)
 EXPORTS = [
-    "ctg_ctx_create", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_ctx_set_ba_levels", "ctg_ctx_set_msm_split", "ctg_sync", "ctg_launch_count",
+    "ctg_ctx_create", "ctg_ctx_device_count", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_ctx_set_ba_levels", "ctg_ctx_set_msm_split", "ctg_sync", "ctg_launch_count",
     "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch",
     "ctg_fr_mul_batch", "ctg_fq_mul_batch", "ctg_imad_peak_probe", "ctg_ntt_fr", "ctg_ntt_fr_dev",
     "ctg_bases_upload_g1", "ctg_bases_upload_g2", "ctg_bases_progression_g1", "ctg_bases_progression_g2",
@@ -143,13 +143,17 @@ class Bases:
 
 
 class Context:
-    """One CUDA device (ctg_ctx).  `stream`: a raw cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+    """One CUDA device (ctg_ctx), or -- device = a list of ids -- a multi-device context: one process driving several GPUs, the
+    prover-path calls (upload_pk, upload_r1cs, prove, bases_*, msm*) shard over them by themselves, everything else runs on
+    the first device.  `stream`: a raw cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream) for the (first) device."""
 
     def __init__(self, device=0, stream=None):
         lib = load()
         self.h = C.c_void_p()
-        ids = (C.c_int * 1)(device)
-        rc = lib.ctg_ctx_create(ids, 1, C.byref(self.h))
+        devs = [int(d) for d in device] if isinstance(device, (list, tuple)) else [int(device)]
+        self.devices = devs
+        ids = (C.c_int * len(devs))(*devs)
+        rc = lib.ctg_ctx_create(ids, len(devs), C.byref(self.h))
         if rc != 0:
             raise CtgError(f"ctg_ctx_create failed with {rc}: no usable sm_100 CUDA device (there is no CPU fallback)")
         if stream is not None:

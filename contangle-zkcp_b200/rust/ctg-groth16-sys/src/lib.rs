@@ -61,6 +61,7 @@ pub struct ctg_timings {
 
 extern "C" {
     pub fn ctg_ctx_create(device_ids: *const c_int, n_devices: c_int, out: *mut *mut ctg_ctx) -> i32;
+    pub fn ctg_ctx_device_count(ctx: *mut ctg_ctx) -> i32;
     pub fn ctg_ctx_destroy(ctx: *mut ctg_ctx);
     pub fn ctg_last_error(ctx: *mut ctg_ctx) -> *const c_char;
     pub fn ctg_ctx_set_stream(ctx: *mut ctg_ctx, cuda_stream: *mut c_void) -> i32;

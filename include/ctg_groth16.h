@@ -100,9 +100,22 @@ typedef struct {
 } ctg_timings;
 
 /* ---- context ---------------------------------------------------------------------- */
-/* One device per context: n_devices must be 1 (multi-GPU runs use one process / context per
- * GPU and exchange 192-byte partial sums, see ctg_msm_g1_partial + ctg_g1_combine). */
+/* n_devices == 1: the context is bound to that GPU.
+ * n_devices in 2..8 (one process, several GPUs of one NVLink / NVSwitch box; peer access between all of them is required):
+ * device_ids[0] is the PRIMARY device -- every entry point without a sharded form (NTT, key generation, codecs, Poseidon, ...)
+ * runs there exactly as on a one-device context -- and the calls on the prover path shard over all devices by themselves:
+ *   ctg_pk_upload      keeps a point-range shard of every query on each device (1/N of the key per GPU)
+ *   ctg_r1cs_upload    replicates the matrices on the devices that compute witness-map chains
+ *   ctg_prove[_batch]  the five MSMs by point range, the three NTT chains on three devices, one exchange of the chains and of the
+ *                      slices of h with cudaMemcpyPeerAsync over NVLink, 1152 B of partial sums per device summed on the primary;
+ *                      no host round trip between the phases; the proof is bit-identical to the one-device proof
+ *   ctg_bases_upload_* / ctg_bases_progression_* / ctg_msm_g1 / ctg_msm_g2 [_dev]   the same for a stand-alone MSM (scalars of
+ *                      the _dev forms live on the primary device; so does the projective result)
+ * A device id may be listed more than once (its shards then share that GPU: no speed-up, but a one-GPU machine can run this path).
+ * Handles made by a multi-device context work with that context only (CTG_ERR_STATE otherwise); the shard / partial entry
+ * points (ctg_pk_upload_shard, ctg_prove_partial, ...) are the one-process-per-GPU form of the same scheme and refuse them. */
 int32_t ctg_ctx_create(const int* device_ids, int n_devices, ctg_ctx** out);
+int32_t ctg_ctx_device_count(ctg_ctx* ctx); /* 1, or the n_devices of a multi-device context */
 void ctg_ctx_destroy(ctg_ctx* ctx);
 const char* ctg_last_error(ctg_ctx* ctx);
 /* Run all work of this context on a caller-owned cudaStream_t (e.g. torch's current stream). */

@@ -410,6 +410,33 @@ def test_prove_batch_matches_single_proofs(ctx):
     dpk.free(); dr.free()
 
 
+@pytest.mark.parametrize("shape,nproofs", [("mulchain1", 5), ("mulchain5", 300), ("mulchain12", 9), ("poe1", 40)])
+def test_prove_batch_fused_chunks(ctx, shape, nproofs):
+    """The fused batch pipeline (one sort / accumulate / reduce per MSM for a whole chunk of proofs; batched SpMV and NTT passes):
+    independent witnesses AND independent (r, s) per proof, more proofs than one chunk holds (300 > 256), the smallest domain (2),
+    a two-pass NTT domain (2^12) and the PoE shape with its skewed witness; every proof equals ctg_prove's, samples equal the oracle's."""
+    def make(seed):
+        if shape.startswith("mulchain"):
+            return S.mul_chain(int(shape[8:]), seed=seed)
+        return S.poe_shape(1, seed=seed, gates=600, bits=256)
+    r1cs, _, _ = make(1)
+    pk, _ = S.progression_pk(ctx, r1cs)
+    dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"])
+    dr = ctx.upload_r1cs(r1cs)
+    zs = np.stack([make(1 + (i % 11))[1] for i in range(nproofs)])
+    rss = ark.fr_mont_from_ints([rnd.randrange(B.R_MOD) for _ in range(2 * nproofs)]).reshape(nproofs, 2, 8)
+    rss[min(3, nproofs - 1), 0] = 0                      # r = 0: arkworks skips B1 (the product r * B1 vanishes either way)
+    out = ctx.prove_batch(dpk, dr, zs, rss)
+    step = max(1, nproofs // 25)
+    for i in list(range(0, nproofs, step)) + [nproofs - 1]:
+        single = ctx.prove(dpk, dr, zs[i], rss[i][0], rss[i][1])
+        assert np.array_equal(out[i], np.concatenate(single)), i
+    for i in (0, min(3, nproofs - 1), nproofs - 1):
+        want = ark.create_proof(pk, r1cs, zs[i], rss[i][0], rss[i][1])
+        assert np.array_equal(out[i], np.concatenate(want)), i
+    dpk.free(); dr.free()
+
+
 @pytest.mark.parametrize("log_n,shards", [(4, 2), (9, 3), (12, 8)])
 def test_prove_sharded_partials_combine(ctx, log_n, shards):
     """The multi-GPU path on one GPU: every shard's ctg_prove_partial, then ctg_prove_combine, equals ctg_prove."""
