@@ -144,6 +144,47 @@ def poe_shape(n_data, seed=0xC0FFEE, gates=7500, bits=512):
     return r1cs, fr_mont(z), z
 
 
+def poe_shape_witnesses(ctx, n_data, count, seed=0xC0FFEE, gates=7500, bits=512):
+    """`count` INDEPENDENT satisfying assignments of PoEShape(n_data) (the matrices of poe_shape do not depend on the seed),
+    as (count, m, 8) Montgomery words -- one per buyer request / ciphertext block (lib/src/seller.rs:136-159,
+    docs/protocol.md:56).  The multiplication chain is advanced for all assignments at once with the device's Fr product
+    (Montgomery images multiply to Montgomery images), everything else is numpy table look-ups."""
+    FR = 0   # CTG_FIELD_FR
+    ADD = 1  # CTG_OP_ADD
+    g = np.random.default_rng(seed ^ (n_data * 0x9E37 + 1))
+    ni = 3 + n_data
+    nw = bits + 2 + gates + 3 * n_data
+    z = np.zeros((count, ni + nw, 8), dtype=np.uint32)
+    tab = fr_mont(list(range(256)))                                        # bytes
+    inv = fr_mont([pow(v, -1, R_MOD) if v else 0 for v in range(256)])
+    z[:, 0] = tab[1]
+
+    def rand_fr(k):
+        w = g.integers(0, 1 << 32, size=(k, 8), dtype=np.uint64).astype(np.uint32)
+        w[:, 7] &= 0x3FFFFFFF                                              # < 2^254 < r: a valid Montgomery image of SOME element
+        return w
+    z[:, 1], z[:, 2] = rand_fr(count), rand_fr(count)
+    w0 = ni
+    z[:, w0:w0 + bits] = tab[g.integers(0, 2, size=(count, bits))]
+    j = w0 + bits
+    a, b = rand_fr(count), rand_fr(count)
+    z[:, j], z[:, j + 1] = a, b
+    j += 2
+    for _ in range(gates):
+        a, b = b, ctx.fr_mul(a, b)
+        z[:, j] = b
+        j += 1
+    mask = b
+    if n_data:
+        m = g.integers(0, 256, size=(count, n_data))
+        z[:, j + 0:j + 3 * n_data:3] = tab[m]
+        z[:, j + 1:j + 3 * n_data:3] = inv[m]
+        z[:, j + 2:j + 3 * n_data:3] = tab[(m == 0).astype(np.int64)]
+        c2 = ctx.field_op(FR, ADD, tab[m].reshape(-1, 8), np.repeat(mask, n_data, axis=0))
+        z[:, 3:3 + n_data] = c2.reshape(count, n_data, 8)
+    return z
+
+
 def r1cs_is_satisfied(r1cs, z):
     """Host check with Python ints (small instances only)."""
     one_m = tuple(fr_mont([1])[0])
@@ -209,3 +250,27 @@ def trapdoor(seed=0xC0FFEE):
     words = {k: fr_mont([v])[0] for k, v in ints.items()}
     words["g1"], words["g2"] = g1_gen_words(), g2_gen_words()
     return words, ints
+
+
+def weighted_sums(sc_words, first_index=0):
+    """(sum_i s_i, sum_i (first_index + i) * s_i) as Python integers for an (n, 8) uint32 array of 256-bit scalars -- numpy on
+    16-bit half-limbs in chunks of 2^20 (every partial dot product stays below 2^63), so that the discrete-log closed form of
+    an MSM over progression bases costs O(n) machine arithmetic even at 2^24 points."""
+    sc = np.ascontiguousarray(sc_words, dtype=np.uint32)
+    n = sc.shape[0]
+    halves = sc.view(np.uint16).reshape(n, 16).astype(np.uint64)
+    plain = [int(x) for x in halves.sum(axis=0, dtype=np.uint64)] if n < (1 << 47) else None
+    weighted = [0] * 16
+    CH = 1 << 20
+    for lo in range(0, n, CH):
+        hi = min(n, lo + CH)
+        idx = np.arange(lo, hi, dtype=np.uint64)          # local index < 2^24 per chunk offset: (idx - lo) < 2^20
+        loc = idx - np.uint64(lo)
+        blk = halves[lo:hi]
+        dots = loc @ blk                                   # < 2^20 * 2^20 * 2^16 = 2^56
+        sums = blk.sum(axis=0, dtype=np.uint64)
+        for k in range(16):
+            weighted[k] += int(dots[k]) + (first_index + lo) * int(sums[k])
+    s0 = sum(v << (16 * k) for k, v in enumerate(plain))
+    s1 = sum(v << (16 * k) for k, v in enumerate(weighted))
+    return s0, s1

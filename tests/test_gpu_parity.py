@@ -437,6 +437,48 @@ def test_prove_batch_fused_chunks(ctx, shape, nproofs):
     dpk.free(); dr.free()
 
 
+def test_poe_shape_witness_batch_satisfies_and_proves(ctx):
+    """ctg.synthetic.poe_shape_witnesses: independent assignments of the PoE shape built with the device's Fr product.  Each must
+    satisfy the R1CS (host big-int check), differ from the others, and prove in a batch to what ctg_prove / the oracle give."""
+    r1cs, _, _ = S.poe_shape(4, gates=120, bits=24)
+    zb = S.poe_shape_witnesses(ctx, 4, 6, seed=77, gates=120, bits=24)
+    assert zb.shape == (6, r1cs["num_instance"] + r1cs["num_witness"], 8)
+    for i in range(6):
+        assert S.r1cs_is_satisfied(r1cs, ark.fr_ints_from_mont(zb[i])), i
+    assert len({zb[i].tobytes() for i in range(6)}) == 6
+    pk, _ = S.progression_pk(ctx, r1cs)
+    dpk = ctx.upload_pk(pk, r1cs["num_instance"], r1cs["num_constraints"])
+    dr = ctx.upload_r1cs(r1cs)
+    rss = ark.fr_mont_from_ints([rnd.randrange(B.R_MOD) for _ in range(12)]).reshape(6, 2, 8)
+    out = ctx.prove_batch(dpk, dr, zb, rss)
+    for i in range(6):
+        assert np.array_equal(out[i], np.concatenate(ctx.prove(dpk, dr, zb[i], rss[i][0], rss[i][1]))), i
+    assert np.array_equal(out[5], np.concatenate(ark.create_proof(pk, r1cs, zb[5], rss[5][0], rss[5][1])))
+    dpk.free(); dr.free()
+
+
+def test_prove_batch_1024_independent_poe_proofs(ctx):
+    """BASELINE.json configs[4] at its stated batch: 1024 independent PoE-shaped assignments (domain 2^13) under one
+    device-resident generated key; sampled proofs equal ctg_prove's, two equal the oracle's, and the batch stays under
+    20 kernel launches per proof."""
+    r1cs, _, _ = S.poe_shape(1)
+    zb = S.poe_shape_witnesses(ctx, 1, 1024, seed=5)
+    dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
+    key_host = dp.download()
+    dpk = dp.to_device_pk()
+    dp.free()
+    dr = ctx.upload_r1cs(r1cs)
+    rss = ark.fr_mont_from_ints([rnd.randrange(B.R_MOD) for _ in range(2048)]).reshape(1024, 2, 8)
+    l0 = ctx.launches
+    out = ctx.prove_batch(dpk, dr, zb, rss)
+    assert (ctx.launches - l0) / 1024 <= 20
+    for i in list(range(0, 1024, 93)) + [1023]:
+        assert np.array_equal(out[i], np.concatenate(ctx.prove(dpk, dr, zb[i], rss[i][0], rss[i][1]))), i
+    for i in (0, 1023):
+        assert np.array_equal(out[i], np.concatenate(ark.create_proof(key_host, r1cs, zb[i], rss[i][0], rss[i][1]))), i
+    dpk.free(); dr.free()
+
+
 @pytest.mark.parametrize("log_n,shards", [(4, 2), (9, 3), (12, 8)])
 def test_prove_sharded_partials_combine(ctx, log_n, shards):
     """The multi-GPU path on one GPU: every shard's ctg_prove_partial, then ctg_prove_combine, equals ctg_prove."""

@@ -133,25 +133,4 @@ def closed_form_proof_arrays(r1cs, td, z, r, s, g1=B.G1_GEN, g2=B.G2_GEN):
     return B.G1.mul(g1, ea), B.G2.mul(g2, eb), B.G1.mul(g1, ec)
 
 
-def weighted_sums(sc_words, first_index=0):
-    """(sum_i s_i, sum_i (first_index + i) * s_i) as Python integers for an (n, 8) uint32 array of 256-bit scalars -- numpy on
-    16-bit half-limbs in chunks of 2^20 (every partial dot product stays below 2^63), so that the discrete-log closed form of
-    an MSM over progression bases costs O(n) machine arithmetic even at 2^24 points."""
-    sc = np.ascontiguousarray(sc_words, dtype=np.uint32)
-    n = sc.shape[0]
-    halves = sc.view(np.uint16).reshape(n, 16).astype(np.uint64)
-    plain = [int(x) for x in halves.sum(axis=0, dtype=np.uint64)] if n < (1 << 47) else None
-    weighted = [0] * 16
-    CH = 1 << 20
-    for lo in range(0, n, CH):
-        hi = min(n, lo + CH)
-        idx = np.arange(lo, hi, dtype=np.uint64)          # local index < 2^24 per chunk offset: (idx - lo) < 2^20
-        loc = idx - np.uint64(lo)
-        blk = halves[lo:hi]
-        dots = loc @ blk                                   # < 2^20 * 2^20 * 2^16 = 2^56
-        sums = blk.sum(axis=0, dtype=np.uint64)
-        for k in range(16):
-            weighted[k] += int(dots[k]) + (first_index + lo) * int(sums[k])
-    s0 = sum(v << (16 * k) for k, v in enumerate(plain))
-    s1 = sum(v << (16 * k) for k, v in enumerate(weighted))
-    return s0, s1
+from ctg.synthetic import weighted_sums  # noqa: E402,F401  (lives beside the generators: bench.py uses it at N > 1)
