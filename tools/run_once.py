@@ -38,5 +38,34 @@ elif what == "prove":
     for _ in range(reps):
         _, tm = ctx.prove(dpk, dr, zm, r, s, timed=True)
         print(tm)
+elif what == "batch":          # `lg` = proofs in the batch; PoE shape n_data = 1 (domain 2^13), generated key
+    r1cs, zm, _ = S.poe_shape(1)
+    dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
+    dpk = dp.to_device_pk()
+    dp.free()
+    dr = ctx.upload_r1cs(r1cs)
+    zb = S.poe_shape_witnesses(ctx, 1, lg, seed=3)
+    rs = S.fr_mont([3 + i for i in range(2 * lg)]).reshape(lg, 2, 8)
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        ctx.prove_batch(dpk, dr, zb, rs)
+        print("prove_batch", lg, "proofs:", (time.perf_counter() - t0) * 1e3, "ms")
+elif what == "setup":          # key generation (fixed_base_kernel, lagrange / qap kernels)
+    r1cs, zm, _ = S.mul_chain(lg)
+    for _ in range(reps):
+        dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
+        dp.free()
+elif what == "te":             # bulk JubJub: shared-base table kernel, per-item kernel, hashed ElGamal
+    d_jj = S.fr_mont([(-10240 * pow(10241, -1, S.R_MOD)) % S.R_MOD])[0]
+    gen = S.fr_mont([8076246640662884909881801758704306714034609987455869804520522091855516602923,
+                     13262374693698910701929044844600465831413122818447359594527400194675274060458])
+    d_gen = torch.from_numpy(gen.view(np.int32).copy()).to(dev)
+    ks = torch.randint(-(1 << 31), (1 << 31) - 1, (n, 8), device=dev, dtype=torch.int32)
+    res = torch.empty((n, 2, 8), device=dev, dtype=torch.int32)
+    for _ in range(reps):
+        ctx.te_mul_batch_dev(d_jj, d_gen.data_ptr(), 1, ks.data_ptr(), n, res.data_ptr())          # te_mul_table_kernel
+    pts = res[: n // 16].contiguous()
+    for _ in range(reps):
+        ctx.te_mul_batch_dev(d_jj, pts.data_ptr(), n // 16, ks.data_ptr(), n // 16, res.data_ptr())   # te_mul_kernel (a base per item)
 torch.cuda.synchronize()
 print("done")
