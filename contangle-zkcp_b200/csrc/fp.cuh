@@ -41,6 +41,13 @@ struct FrParams {
   }
 };
 
+#if defined(__CUDACC__)
+// -r^-1 mod 2^32 of Fr (= 2^32 - 1) as a constant-bank word.  Fp<FrParams>::redc_row forms m = E[0] * this word with a real IMAD on
+// the device: when m is produced by the ALU instead (the strength-reduced negation), ptxas 12.9 splits EVERY mad.lo.cc / madc.hi.cc
+// pair of the row into IMAD.X + IMAD.HI.U32.X, and an IMAD.HI costs the FMA pipe as much as the paired IMAD.WIDE (two issue slots,
+// profiles/r01_pipe_probe.txt): 304 slots per Montgomery product instead of 233.
+static __constant__ uint32_t kFrNegInvBank = 0xffffffffu;
+#endif
 struct FqParams {
   static constexpr int N = 12;
   static constexpr uint32_t INV = 0xfffcfffdu;  // -p^-1 mod 2^32
@@ -125,6 +132,37 @@ template <class P> struct alignas(16) Fp {
   // --- Montgomery product ------------------------------------------------------------
   // add m*p into (E at limbs 0.., O at limbs 1..); leaves E[0] == 0
   CTG_HD static void redc_row(uint32_t* E, uint32_t* O) {
+    if constexpr (P::mod(0) == 1u && P::mod(1) == 0xffffffffu && P::INV == 0xffffffffu && N % 2 == 0) {
+      // Fr: the modulus ends in 2^64 - 2^32 + 1, so m = -E[0] and the two low limbs of m * p need no multiplier:
+      //   E[0] + m * p = (m 2^32 - k) 2^32 + m * (p >> 64) 2^64,   k = m - [m != 0]
+      // i.e. a 64-bit value V added at limb 1 and N - 2 paired products (48 IMAD.WIDE per Montgomery product for this half).
+#if defined(__CUDA_ARCH__)
+      const uint32_t m = ptx::mul_lo(E[0], kFrNegInvBank);   // see kFrNegInvBank: keeps the pairs below as IMAD.WIDE
+#else
+      const uint32_t m = 0u - E[0];
+#endif
+      const uint32_t k = m - (m != 0u ? 1u : 0u);
+      const uint32_t vlo = ptx::sub_cc(0u, k);
+      const uint32_t vhi = ptx::subc(m, 0u);
+      O[0] = ptx::add_cc(O[0], vlo);
+      O[1] = ptx::addc_cc(O[1], vhi);
+#pragma unroll
+      for (int j = 3; j < N; j += 2) {
+        O[j - 1] = ptx::madc_lo_cc(P::mod(j), m, O[j - 1]);
+        if (j == N - 1) O[j] = ptx::madc_hi(P::mod(j), m, O[j]);
+        else O[j] = ptx::madc_hi_cc(P::mod(j), m, O[j]);
+      }
+      E[0] = 0;
+      E[2] = ptx::mad_lo_cc(P::mod(2), m, E[2]);
+      E[3] = ptx::madc_hi_cc(P::mod(2), m, E[3]);
+#pragma unroll
+      for (int j = 4; j < N; j += 2) {
+        E[j] = ptx::madc_lo_cc(P::mod(j), m, E[j]);
+        E[j + 1] = ptx::madc_hi_cc(P::mod(j), m, E[j + 1]);
+      }
+      O[N - 1] = ptx::addc(O[N - 1], 0);
+      return;
+    }
     const uint32_t m = ptx::mul_lo(E[0], P::INV);
     O[0] = ptx::mad_lo_cc(P::mod(1), m, O[0]);
     O[1] = ptx::madc_hi_cc(P::mod(1), m, O[1]);

@@ -18,7 +18,10 @@
 // and its bit-reversed output is consumed by an MSM whose bases were permuted at key upload.
 // Coset shifts (g = 7), the 1/n of the inverse transform and their product are fused into the
 // first load / last store of a pass through per-domain power tables.
+#include <cuda.h>   // CUtensorMap and the cuTensorMapEncodeTiled prototype (resolved at run time, libcuda is not linked)
+
 #include <algorithm>
+#include <cstdlib>
 
 #include "ctg_internal.h"
 
@@ -168,6 +171,215 @@ __global__ void __launch_bounds__(kThreads) ntt_pass_kernel(Fr* __restrict__ dat
   }
 }
 
+// ======================================================================================================================
+// Blackwell-native pass kernel (the default for tiles of >= 32 elements): the tile moves between HBM and shared memory as ONE
+// tensor-map copy in each direction (cp.async.bulk.tensor = UTMALDG / UTMASTG; the copy engine computes the strided addresses:
+// a strided pass is a 3-D box of 256 rows x C columns, a contiguous pass a 2-D box), completion through an mbarrier.  The tensor
+// map asks for the 128-byte swizzle, so that four consecutive elements (one 128-byte line) land XOR-permuted by the line number
+// and the warp-wide 16-byte accesses of the butterfly rounds are bank-conflict free.  The butterflies run in REGISTERS: a
+// thread owns 8 elements for three levels (radix-8 round: 12 butterflies, 7 distinct twiddles) between two shared-memory
+// exchanges, instead of one shared-memory round trip, one twiddle load and one index computation per butterfly and level.
+// Two CTAs (2 x 64 KB) are resident per SM: while one computes, the other's tile is in flight -- the double buffer.
+// Results are bit-identical to ntt_pass_kernel (same butterflies, same twiddles, exact field arithmetic).
+static constexpr int kTmaMinLogTile = 5;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+               ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+// byte offset of half `h` (16 bytes) of tile element e in the 128B-swizzled tile: line = e / 4, chunk ^= line % 8
+__device__ __forceinline__ uint32_t sw_off(uint32_t e, uint32_t h) {
+  const uint32_t line = e >> 2;
+  return (line << 7) | (((((e & 3u) << 1) | h) ^ (line & 7u)) << 4);
+}
+__device__ __forceinline__ Fr lds_fr(const unsigned char* sm, uint32_t e) {
+  const uint4 a = *reinterpret_cast<const uint4*>(sm + sw_off(e, 0));
+  const uint4 b = *reinterpret_cast<const uint4*>(sm + sw_off(e, 1));
+  Fr r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ void sts_fr(unsigned char* sm, uint32_t e, const Fr& r) {
+  *reinterpret_cast<uint4*>(sm + sw_off(e, 0)) = make_uint4(r.v[0], r.v[1], r.v[2], r.v[3]);
+  *reinterpret_cast<uint4*>(sm + sw_off(e, 1)) = make_uint4(r.v[4], r.v[5], r.v[6], r.v[7]);
+}
+
+struct TileGeom {
+  int strided, log_C, log_cpb;
+  uint32_t j0;
+};
+// table position of the twiddle of the butterfly whose upper operand sits at tile-local offset w inside its butterfly block
+__device__ __forceinline__ uint64_t tw_pos(const TileGeom& g, uint32_t w) {
+  return g.strided ? ((uint64_t)(w >> g.log_C) << g.log_cpb) + g.j0 + (w & ((1u << g.log_C) - 1)) : (uint64_t)w;
+}
+
+// One round of K butterfly levels on register-resident groups of 2^K elements spaced 2^g apart in the tile.
+// DIF: levels run from log_h = log_h0 down; DIT: from log_h0 up.  `tile` elements, all threads of the CTA take part.
+template <int K, bool DIT>
+__device__ __forceinline__ void ntt_round(unsigned char* sm, const NttPass& p, const TileGeom& geo, int g, int log_h0, int tile) {
+  constexpr int R = 1 << K;
+  for (uint32_t grp = threadIdx.x; grp < (uint32_t)(tile >> K); grp += kThreads) {
+    const uint32_t low = grp & ((1u << g) - 1);
+    const uint32_t i0 = ((grp >> g) << (g + K)) | low;
+    Fr x[R];
+#pragma unroll
+    for (int m = 0; m < R; m++) x[m] = lds_fr(sm, i0 + ((uint32_t)m << g));
+#pragma unroll
+    for (int l = 0; l < K; l++) {
+      const int md = DIT ? (1 << l) : (1 << (K - 1 - l));           // register distance of the pair
+      const int log_h = DIT ? log_h0 + l : log_h0 - l;
+      const int tw_shift = p.log_n - 1 - (log_h + geo.log_cpb);
+#pragma unroll
+      for (int q = 0; q < md; q++) {
+        const Fr tw = ldg_fr(p.tw + (tw_pos(geo, low | ((uint32_t)q << g)) << tw_shift));
+#pragma unroll
+        for (int hb = 0; hb < R / (2 * md); hb++) {
+          const int m = hb * 2 * md + q;
+          if (DIT) {
+            const Fr tv = x[m + md] * tw;
+            const Fr u = x[m];
+            x[m] = u + tv;
+            x[m + md] = u - tv;
+          } else {
+            const Fr u = x[m], v = x[m + md];
+            x[m] = u + v;
+            x[m + md] = (u - v) * tw;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < R; m++) sts_fr(sm, i0 + ((uint32_t)m << g), x[m]);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) ntt_pass_tma_kernel(const __grid_constant__ CUtensorMap tmap, NttPass p) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t mbar;
+  unsigned char* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // the swizzle pattern is a function of address bits 7..9
+  const int tile = 1 << p.log_tile;
+  TileGeom geo;
+  geo.log_cpb = p.log_blk - p.S;
+  geo.log_C = p.log_tile - p.S;
+  geo.strided = geo.log_cpb > geo.log_C;
+  geo.j0 = 0;
+  const uint64_t tile_id = blockIdx.x;
+  uint64_t base;   // element address (inside this transform) of tile-local index 0
+  int c1, c2;      // tensor coordinates of the tile
+  if (geo.strided) {
+    const uint64_t q0 = tile_id << geo.log_C;
+    const uint64_t b = q0 >> geo.log_cpb;
+    geo.j0 = (uint32_t)(q0 & ((1ull << geo.log_cpb) - 1));
+    base = (b << p.log_blk) + geo.j0;
+    c1 = (int)(geo.j0 >> 2);
+    c2 = (int)(((uint64_t)blockIdx.y << (p.log_n - geo.log_cpb)) + (b << p.S));
+  } else {
+    base = tile_id << p.log_tile;
+    c1 = (int)((((uint64_t)blockIdx.y << p.log_n) + base) >> 2);
+    c2 = 0;
+  }
+  const int lines = tile >> 2, box_lines = lines < 256 ? lines : 256;
+  const uint32_t sm_a = smem_u32(sm);
+  if (threadIdx.x == 0) mbar_init(&mbar, 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(&mbar, (uint32_t)tile * 32u);
+    if (geo.strided) tma_load_3d(sm_a, &tmap, &mbar, 0, c1, c2);
+    else
+      for (int l = 0; l < lines; l += box_lines) tma_load_2d(sm_a + (uint32_t)l * 128u, &tmap, &mbar, 0, c1 + l);
+  }
+  mbar_wait(&mbar, 0);
+
+  auto addr_of = [&](uint32_t e) -> uint64_t {
+    return geo.strided ? base + ((uint64_t)(e >> geo.log_C) << geo.log_cpb) + (e & ((1u << geo.log_C) - 1)) : base + e;
+  };
+  if (p.pre_tab) {
+    for (uint32_t e = threadIdx.x; e < (uint32_t)tile; e += kThreads) {
+      const uint64_t a = addr_of(e);
+      sts_fr(sm, e, lds_fr(sm, e) * ldg_fr(p.pre_tab + (p.pre_bitrev ? bitrev_idx(a, p.log_n) : a)));
+    }
+    __syncthreads();
+  }
+
+  // levels t = 0 .. S-1 in rounds of up to three (rounds of two at the end so that no round is a single level when S >= 2)
+  const int dbase = geo.strided ? geo.log_C : geo.log_cpb;   // log2 of the tile-local butterfly distance at log_h = 0
+  int t = 0;
+  while (t < p.S) {
+    const int rem = p.S - t;
+    const int K = rem > 4 ? 3 : rem == 4 ? 2 : rem;
+    // DIF walks log_h = S-1-t downwards (spacing = the smallest distance of the round); DIT walks log_h = t upwards
+    const int log_h0 = p.dit ? t : p.S - 1 - t;
+    const int g = dbase + (p.dit ? log_h0 : log_h0 - (K - 1));
+    if (p.dit) {
+      if (K == 3) ntt_round<3, true>(sm, p, geo, g, log_h0, tile);
+      else if (K == 2) ntt_round<2, true>(sm, p, geo, g, log_h0, tile);
+      else ntt_round<1, true>(sm, p, geo, g, log_h0, tile);
+    } else {
+      if (K == 3) ntt_round<3, false>(sm, p, geo, g, log_h0, tile);
+      else if (K == 2) ntt_round<2, false>(sm, p, geo, g, log_h0, tile);
+      else ntt_round<1, false>(sm, p, geo, g, log_h0, tile);
+    }
+    t += K;
+    __syncthreads();
+  }
+
+  if (p.post_tab || p.post_const) {
+    for (uint32_t e = threadIdx.x; e < (uint32_t)tile; e += kThreads) {
+      Fr v = lds_fr(sm, e);
+      if (p.post_tab) {
+        const uint64_t a = addr_of(e);
+        v = v * ldg_fr(p.post_tab + (p.post_bitrev ? bitrev_idx(a, p.log_n) : a));
+      } else {
+        v = v * p.post_c;
+      }
+      sts_fr(sm, e, v);
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes above -> visible to the copy engine
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (geo.strided) tma_store_3d(&tmap, sm_a, 0, c1, c2);
+    else
+      for (int l = 0; l < lines; l += box_lines) tma_store_2d(&tmap, sm_a + (uint32_t)l * 128u, 0, c1 + l);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // shared memory must outlive the copy
+  }
+}
+
 __global__ void bitrev_permute_kernel(Fr* data, int log_n) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (1ull << log_n)) return;
@@ -275,7 +487,10 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
   CTG_TRY(fill_pow_table(ctx, d.gipow_n, n, gi, d.n_inv, st));
   // a per-device attribute: once per context, not once per process (a multi-device context has one context per GPU)
   if (ctx->domains.empty())
+  {
     CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32));
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
+  }
   CTG_CUDA(ctx, cudaStreamSynchronize(st));  // other streams (prover lanes) may use the tables next
   ctx->domains[log_n] = d;
   *out = &ctx->domains[log_n];
@@ -286,6 +501,52 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
 int32_t fr_pow_table(ctg_ctx* ctx, Fr* d_out, uint64_t n, const Fr& base, const Fr& scale, cudaStream_t st) { return fill_pow_table(ctx, d_out, n, base, scale, st); }
 Fr fr_root_of_unity(int log_n) { return host_root_of_unity(log_n); }
 Fr fr_from_u64(uint64_t x) { return host_fr_from_u64(x); }
+
+// ---- tensor maps for ntt_pass_tma_kernel.  cuTensorMapEncodeTiled is a pure host function of the driver; it is resolved through
+// the runtime (cudaGetDriverEntryPoint), so the library still links against libcudart only.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) f = nullptr;
+    cudaGetLastError();
+    return (EncodeTiledFn)f;
+  }();
+  return fn;
+}
+static bool ntt_legacy() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CTG_NTT_LEGACY"); v = e && *e == '1'; }
+  return v != 0;
+}
+// The transform(s) at d seen as lines of 128 bytes (four elements).  Strided pass: dims (32 words, cpb / 4 line columns, rows of all
+// sub-transforms of all batch entries), box = (32, C / 4, 2^S); contiguous pass: dims (32 words, lines), box = (32, min(256, tile / 4)).
+static int32_t make_tile_map(ctg_ctx* ctx, CUtensorMap* tm, Fr* d, const NttPass& p, uint32_t batch) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return fail(ctx, CTG_ERR_CUDA, "ntt: the driver does not export cuTensorMapEncodeTiled");
+  const int log_cpb = p.log_blk - p.S, log_C = p.log_tile - p.S;
+  const cuuint32_t ones[3] = {1, 1, 1};
+  CUresult r;
+  if (log_cpb > log_C) {
+    const cuuint64_t dims[3] = {32, 1ull << (log_cpb - 2), (cuuint64_t)batch << (p.log_n - log_cpb)};
+    const cuuint64_t strides[2] = {128, 32ull << log_cpb};
+    const cuuint32_t box[3] = {32, 1u << (log_C - 2), 1u << p.S};
+    r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, d, dims, strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    const cuuint64_t lines = ((cuuint64_t)batch << p.log_n) >> 2;
+    const cuuint64_t dims[2] = {32, lines};
+    const cuuint64_t strides[1] = {128};
+    const cuuint32_t tl = 1u << (p.log_tile - 2);
+    const cuuint32_t box[2] = {32, tl < 256 ? tl : 256};
+    r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, d, dims, strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (r != CUDA_SUCCESS) return fail(ctx, CTG_ERR_CUDA, "ntt: cuTensorMapEncodeTiled failed with " + std::to_string((int)r));
+  return CTG_OK;
+}
 
 struct PassGeom { int log_blk, S; };
 // DIF order (large sub-transforms first).  DIT uses the same list reversed.
@@ -332,7 +593,13 @@ static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit,
     p.post_c = f.post_c;
     unsigned blocks = (unsigned)(n >> p.log_tile);
     size_t smem = ((size_t)1 << p.log_tile) * 32;
-    ntt_pass_kernel<<<dim3(blocks, batch), kThreads, smem, st>>>(d, p);
+    if (p.log_tile >= kTmaMinLogTile && !ntt_legacy() && (reinterpret_cast<uintptr_t>(d) & 15) == 0) {
+      CUtensorMap tm;
+      CTG_TRY(make_tile_map(ctx, &tm, d, p, batch));
+      ntt_pass_tma_kernel<<<dim3(blocks, batch), kThreads, smem + 1024, st>>>(tm, p);
+    } else {
+      ntt_pass_kernel<<<dim3(blocks, batch), kThreads, smem, st>>>(d, p);
+    }
     CTG_KERNEL_CHECK(ctx);
   }
   return CTG_OK;

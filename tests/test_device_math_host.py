@@ -46,6 +46,21 @@ def test_field_ops_match_oracle(hm, field):
         assert np.array_equal(out, want), op
 
 
+def test_fr_mul_special_form_reduction_rows(hm):
+    """Fp<FrParams>::redc_row exploits r = ... 2^64 - 2^32 + 1 (m = -E[0], the two low limbs of m * r without a multiplier): operands
+    whose limbs are drawn from {0, 1, 2^31, 2^32 - 1} drive the row through m = 0, m = 1, m = 2^32 - 1 and the carry out of limb 1."""
+    limbs = [0, 1, 0x80000000, 0xFFFFFFFF]
+    vals = [sum(rnd.choice(limbs) << (32 * i) for i in range(8)) % B.R_MOD for _ in range(4000)]
+    a = ark.ints_to_words(vals, 8)
+    b = ark.ints_to_words(vals[::-1], 8)
+    out = np.zeros_like(a)
+    hm.hm_fr_mul(_p(a), _p(b), _p(out), C.c_uint64(len(vals)))
+    assert np.array_equal(out, ark.fr_mul(a, b))
+    one = ark.ints_to_words([1] * len(vals), 8)              # from_mont: rows where only E[0] of the first row is non-zero
+    hm.hm_fr_mul(_p(a), _p(one), _p(out), C.c_uint64(len(vals)))
+    assert np.array_equal(out, ark.fr_mul(a, one))
+
+
 def test_fr_mont_conversions(hm):
     vals = _edge(B.R_MOD, 50)
     a = ark.ints_to_words(vals, 8)
