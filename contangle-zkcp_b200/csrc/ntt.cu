@@ -287,7 +287,10 @@ __device__ __forceinline__ void ntt_round(unsigned char* sm, const NttPass& p, c
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 2) ntt_pass_tma_kernel(const __grid_constant__ CUtensorMap tmap, NttPass p) {
+// MAXK = 3: radix-8 rounds, 128 registers, two CTAs per SM (16 warps).  MAXK = 2: radix-4 rounds, 80 registers, three CTAs per SM
+// (24 warps): one more shared-memory exchange per pass for half as many live registers.  CTG_NTT_RADIX4=1 selects the latter.
+template <int MAXK>
+__global__ void __launch_bounds__(kThreads, MAXK == 3 ? 2 : 3) ntt_pass_tma_kernel(const __grid_constant__ CUtensorMap tmap, NttPass p) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mbar;
   unsigned char* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // the swizzle pattern is a function of address bits 7..9
@@ -340,16 +343,16 @@ __global__ void __launch_bounds__(kThreads, 2) ntt_pass_tma_kernel(const __grid_
   int t = 0;
   while (t < p.S) {
     const int rem = p.S - t;
-    const int K = rem > 4 ? 3 : rem == 4 ? 2 : rem;
+    const int K = MAXK == 3 ? (rem > 4 ? 3 : rem == 4 ? 2 : rem) : (rem >= 2 ? 2 : 1);
     // DIF walks log_h = S-1-t downwards (spacing = the smallest distance of the round); DIT walks log_h = t upwards
     const int log_h0 = p.dit ? t : p.S - 1 - t;
     const int g = dbase + (p.dit ? log_h0 : log_h0 - (K - 1));
     if (p.dit) {
-      if (K == 3) ntt_round<3, true>(sm, p, geo, g, log_h0, tile);
+      if (MAXK == 3 && K == 3) ntt_round<MAXK, true>(sm, p, geo, g, log_h0, tile);
       else if (K == 2) ntt_round<2, true>(sm, p, geo, g, log_h0, tile);
       else ntt_round<1, true>(sm, p, geo, g, log_h0, tile);
     } else {
-      if (K == 3) ntt_round<3, false>(sm, p, geo, g, log_h0, tile);
+      if (MAXK == 3 && K == 3) ntt_round<MAXK, false>(sm, p, geo, g, log_h0, tile);
       else if (K == 2) ntt_round<2, false>(sm, p, geo, g, log_h0, tile);
       else ntt_round<1, false>(sm, p, geo, g, log_h0, tile);
     }
@@ -489,7 +492,8 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
   if (ctx->domains.empty())
   {
     CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32));
-    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
   }
   CTG_CUDA(ctx, cudaStreamSynchronize(st));  // other streams (prover lanes) may use the tables next
   ctx->domains[log_n] = d;
@@ -515,6 +519,11 @@ static EncodeTiledFn encode_tiled_fn() {
     return (EncodeTiledFn)f;
   }();
   return fn;
+}
+static bool ntt_radix4() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CTG_NTT_RADIX4"); v = e && *e == '1'; }
+  return v != 0;
 }
 static bool ntt_legacy() {
   static int v = -1;
@@ -596,7 +605,8 @@ static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit,
     if (p.log_tile >= kTmaMinLogTile && !ntt_legacy() && (reinterpret_cast<uintptr_t>(d) & 15) == 0) {
       CUtensorMap tm;
       CTG_TRY(make_tile_map(ctx, &tm, d, p, batch));
-      ntt_pass_tma_kernel<<<dim3(blocks, batch), kThreads, smem + 1024, st>>>(tm, p);
+      if (ntt_radix4()) ntt_pass_tma_kernel<2><<<dim3(blocks, batch), kThreads, smem + 1024, st>>>(tm, p);
+      else ntt_pass_tma_kernel<3><<<dim3(blocks, batch), kThreads, smem + 1024, st>>>(tm, p);
     } else {
       ntt_pass_kernel<<<dim3(blocks, batch), kThreads, smem, st>>>(d, p);
     }
