@@ -133,27 +133,27 @@ template <class P> struct alignas(16) Fp {
   // add m*p into (E at limbs 0.., O at limbs 1..); leaves E[0] == 0
   CTG_HD static void redc_row(uint32_t* E, uint32_t* O) {
     if constexpr (P::mod(0) == 1u && P::mod(1) == 0xffffffffu && P::INV == 0xffffffffu && N % 2 == 0) {
-      // Fr: the modulus ends in 2^64 - 2^32 + 1, so m = -E[0] and the two low limbs of m * p need no multiplier:
-      //   E[0] + m * p = (m 2^32 - k) 2^32 + m * (p >> 64) 2^64,   k = m - [m != 0]
-      // i.e. a 64-bit value V added at limb 1 and N - 2 paired products (48 IMAD.WIDE per Montgomery product for this half).
+      // Fr: the modulus ends in 2^64 - 2^32 + 1 and -r^-1 = 2^32 - 1.  Limb 0 of m * r is m itself (one add that clears E[0] and
+      // carries into limb 1); limb 1 is multiplied by the all-ones word FROM THE CONSTANT BANK so that it stays a paired product.
+      // 56 IMAD.WIDE + 8 IMAD per Montgomery product for this half and three carry-chain adds per row.  (Spelling the two low limbs
+      // out with adds alone saves 8 IMAD.WIDE but puts five dependent ALU instructions in front of every row: slower, measured.)
 #if defined(__CUDA_ARCH__)
-      const uint32_t m = ptx::mul_lo(E[0], kFrNegInvBank);   // see kFrNegInvBank: keeps the pairs below as IMAD.WIDE
+      const uint32_t allones = kFrNegInvBank;                // see kFrNegInvBank: keeps the pairs below as IMAD.WIDE
 #else
-      const uint32_t m = 0u - E[0];
+      const uint32_t allones = 0xffffffffu;
 #endif
-      const uint32_t k = m - (m != 0u ? 1u : 0u);
-      const uint32_t vlo = ptx::sub_cc(0u, k);
-      const uint32_t vhi = ptx::subc(m, 0u);
-      O[0] = ptx::add_cc(O[0], vlo);
-      O[1] = ptx::addc_cc(O[1], vhi);
+      const uint32_t m = ptx::mul_lo(E[0], allones);
+      O[0] = ptx::mad_lo_cc(allones, m, O[0]);
+      O[1] = ptx::madc_hi_cc(allones, m, O[1]);
 #pragma unroll
       for (int j = 3; j < N; j += 2) {
         O[j - 1] = ptx::madc_lo_cc(P::mod(j), m, O[j - 1]);
         if (j == N - 1) O[j] = ptx::madc_hi(P::mod(j), m, O[j]);
         else O[j] = ptx::madc_hi_cc(P::mod(j), m, O[j]);
       }
-      E[0] = 0;
-      E[2] = ptx::mad_lo_cc(P::mod(2), m, E[2]);
+      E[0] = ptx::add_cc(E[0], m);
+      E[1] = ptx::addc_cc(E[1], 0u);
+      E[2] = ptx::madc_lo_cc(P::mod(2), m, E[2]);
       E[3] = ptx::madc_hi_cc(P::mod(2), m, E[3]);
 #pragma unroll
       for (int j = 4; j < N; j += 2) {
