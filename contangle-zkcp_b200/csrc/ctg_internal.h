@@ -79,7 +79,7 @@ struct ProveLane {
   cudaEvent_t ev_t[16];   // stage timers
 };
 static constexpr int kMaxLanes = 4;
-struct LaneBufs { Fr* d_z; Fr* d_abc; G1XYZZ* d_g1; G2XYZZ* d_g2; ctg_proof* d_proof; };
+struct LaneBufs { Fr* d_z; Fr* d_abc; G1XYZZ* d_g1; G2XYZZ* d_g2; ctg_proof* d_proof; G1XYZZ* d_early; };
 }  // namespace ctg
 
 #include <condition_variable>
@@ -168,6 +168,9 @@ struct ctg_pk {
   uint64_t l_lo = 0, l_cnt = 0;      // of l (num_witness positions)
   uint64_t h_lo = 0, h_cnt = 0;      // of h_ext (n positions, bit-reversed order)
   ctg::Bases a_ext, b1_ext, b2_ext, l, h_ext;
+  // small whole keys (domain <= 2^15, library-chosen windows): a second copy of the five tables laid out for the throughput-optimal
+  // window of ctg_prove_batch (wider windows, more precomputed multiples; a few tens of MB) -- ctg_prove keeps the latency-optimal one
+  ctg_pk* batch_twin = nullptr;
   std::vector<ctg_pk*> parts;        // multi-device context: one shard per device (the members above are then unused)
 };
 struct ctg_r1cs {
@@ -245,7 +248,7 @@ void params_free(ctg_params* p);
 int32_t params_alloc(ctg_ctx* ctx, uint64_t ni, uint64_t nw, uint64_t nc, uint64_t n, ctg_params** out);   // device arrays sized, contents undefined
 
 // msm_g1.cu / msm_g2.cu
-MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes);
+MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes, bool batch_throughput = false);
 // batch / vec_stride / sorted: see MsmHost::run (msm.cuh)
 int32_t msm_g1_run(ctg_ctx* ctx, MsmWorkspace& ws, const Bases& bases, const uint32_t* d_scalars, uint64_t n, bool scalars_mont,
                    G1XYZZ* d_out, cudaStream_t st, float* stage_ms, uint32_t batch = 1, uint64_t vec_stride = 0, const MsmWorkspace* sorted = nullptr);

@@ -12,7 +12,7 @@ namespace ctg {
 //   window combine        c * (sets - 1) sequential doublings at ~12 us each (one thread).
 // Windows are signed, so c bits need 2^(c-1) buckets.  c <= 21 keeps the bucket-index scan within 1023 tiles.
 // copies_wanted = 0: keep as many precomputed multiples 2^(c G j) P as fit a 12 GiB table.
-MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes) {
+MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t point_bytes, bool batch_throughput) {
   MsmPlan best{};
   double best_cost = -1;
   const double budget = 12.0 * 1024 * 1024 * 1024;
@@ -32,8 +32,18 @@ MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t poin
     p.nbuckets_per_set = 1u << (c - 1);
     const double nb = (double)p.nsets * p.nbuckets_per_set;
     if (c_override <= 0 && (nb > 2097152.0 || (double)nn * p.nwin >= 4294967296.0)) continue;
-    const double red = p.nbuckets_per_set > 65536u ? 0.0012 * nb : 0.0003 * nb;   // chunked running sums only above 2^16 buckets per set
-    double cost = 0.0004 * p.nwin * (double)nn + red + 32.0 * c + 12.0 * c * (p.nsets - 1);
+    double red = p.nbuckets_per_set > 65536u ? 0.0012 * nb : 0.0003 * nb;   // chunked running sums only above 2^16 buckets per set
+    double lat = 32.0 * c + 12.0 * c * (p.nsets - 1);
+    if (batch_throughput) {
+      // The plan of the batch twin of a small key (prove.cu pk_upload): ctg_prove_batch reduces the buckets of a whole chunk of
+      // proofs with one launch per level, so the serial depth is paid once per chunk while the per-bucket work (zero fill,
+      // fix-up, two additions, scan) is paid once per proof.  Measured on B200 with 1020 PoE-shaped proofs per call
+      // (tools/run_once.py batch, CBITS sweep): 0.003 us per bucket; c = 12 .. 13 gives 0.47 ms per proof against 0.61 ms with
+      // the latency-optimal window -- which a lone proof keeps (the same sweep costs a lone 2^13 proof 5.8 -> 7.7 ms).
+      red = 0.003 * nb;
+      lat *= 0.1;
+    }
+    double cost = 0.0004 * p.nwin * (double)nn + red + lat;
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = p; }
   }
   return best;

@@ -136,6 +136,34 @@ __global__ void __launch_bounds__(96) finalize_kernel(FinalizeIn in, ctg_proof* 
   }
 }
 
+// The two scalar multiplications of the assembly, s * A and r * B1, are 255 dependent doublings each (about 1.4 ms for a lone
+// thread).  A one-GPU proof therefore launches each on the stream of ITS MSM as soon as that MSM is done -- they then run under
+// the G2 MSM, which finishes last -- and the closing kernel only adds four points and converts three to affine.
+__global__ void __launch_bounds__(32) scalar_mul_g1_kernel(const G1XYZZ* p, Fr k_mont, G1XYZZ* out) {
+  if (threadIdx.x == 0) {
+    Fr k = k_mont.from_mont();
+    *out = xyzz_mul(*p, k.v);
+  }
+}
+struct FinalizeSumIn { const G1XYZZ *a, *sa, *rb1, *l, *h; const G2XYZZ* b2; };
+__global__ void __launch_bounds__(96) finalize_sum_kernel(FinalizeSumIn in, ctg_proof* out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane != 0) return;
+  if (warp == 0) {
+    G1XYZZ c = xyzz_add(*in.sa, *in.rb1);
+    c = xyzz_add(c, *in.l);
+    c = xyzz_add(c, *in.h);
+    G1Affine ca = xyzz_to_affine(c);
+    *reinterpret_cast<G1Affine*>(&out->c) = ca;
+  } else if (warp == 1) {
+    G1Affine aa = xyzz_to_affine(*in.a);
+    *reinterpret_cast<G1Affine*>(&out->a) = aa;
+  } else {
+    G2Affine b = xyzz_to_affine(*in.b2);
+    *reinterpret_cast<G2Affine*>(&out->b) = b;
+  }
+}
+
 // one block per proof of a batch: results laid out a[p], b1[p], l[p], h[p], b2[p]; (r, s) at rs[2p], rs[2p + 1]
 struct FinalizeBatchIn { const G1XYZZ *a, *b1, *l, *h; const G2XYZZ* b2; const Fr* rs; };
 __global__ void __launch_bounds__(96) finalize_batch_kernel(FinalizeBatchIn in, ctg_proof* out) {
@@ -173,10 +201,10 @@ __global__ void __launch_bounds__(96) finalize_batch_kernel(FinalizeBatchIn in, 
 static void free_bases(Bases& b) { if (b.pts) cudaFree(b.pts); b.pts = nullptr; }
 
 template <class A>
-static int32_t make_bases(ctg_ctx* ctx, Bases& out, int group, uint64_t n, int copies, int c_bits) {
+static int32_t make_bases(ctg_ctx* ctx, Bases& out, int group, uint64_t n, int copies, int c_bits, bool batch_throughput = false) {
   out.group = group;
   out.n = n;
-  out.plan = msm_make_plan(n, copies, c_bits, sizeof(A));
+  out.plan = msm_make_plan(n, copies, c_bits, sizeof(A), batch_throughput);
   out.pts = nullptr;
   if (n * (uint64_t)out.plan.copies >= (1ull << 31)) return fail(ctx, CTG_ERR_INVALID, "pk_upload: query length * precomputed copies must be < 2^31 (ask for fewer copies)");
   size_t bytes = (size_t)out.plan.copies * (n ? n : 1) * sizeof(A);
@@ -214,7 +242,7 @@ static void shard_range(uint64_t total, uint64_t lo_num, uint64_t hi_num, uint64
   *cnt = b - a;
 }
 
-int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, uint64_t lo_num, uint64_t hi_num, uint64_t den, ctg_pk** out) {
+static int32_t pk_upload_impl(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, uint64_t lo_num, uint64_t hi_num, uint64_t den, bool tp, ctg_pk** out) {
   if (!v || !out) return fail(ctx, CTG_ERR_INVALID, "pk_upload: null argument");
   if (den < 1 || lo_num > hi_num || hi_num > den) return fail(ctx, CTG_ERR_INVALID, "pk_upload: bad shard range (need 0 <= lo <= hi <= den, den >= 1)");
   const int shard_index = lo_num == 0 ? 0 : 1, shard_count = (lo_num == 0 && hi_num == den) ? 1 : 2;   // only "whole key or not" matters downstream
@@ -236,11 +264,11 @@ int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, 
   memset(&pk->a_ext, 0, sizeof(Bases)); memset(&pk->b1_ext, 0, sizeof(Bases)); memset(&pk->b2_ext, 0, sizeof(Bases));
   memset(&pk->l, 0, sizeof(Bases)); memset(&pk->h_ext, 0, sizeof(Bases));
   int32_t rc;
-  if ((rc = make_bases<G1Affine>(ctx, pk->a_ext, 1, pk->ext_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G1Affine>(ctx, pk->b1_ext, 1, pk->ext_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G2Affine>(ctx, pk->b2_ext, 2, pk->ext_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G1Affine>(ctx, pk->l, 1, pk->l_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
-  if ((rc = make_bases<G1Affine>(ctx, pk->h_ext, 1, pk->h_cnt, copies, c_bits)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->a_ext, 1, pk->ext_cnt, copies, c_bits, tp)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->b1_ext, 1, pk->ext_cnt, copies, c_bits, tp)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G2Affine>(ctx, pk->b2_ext, 2, pk->ext_cnt, copies, c_bits, tp)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->l, 1, pk->l_cnt, copies, c_bits, tp)) != CTG_OK) return cleanup(rc);
+  if ((rc = make_bases<G1Affine>(ctx, pk->h_ext, 1, pk->h_cnt, copies, c_bits, tp)) != CTG_OK) return cleanup(rc);
 #define PK_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { ctx->last_error = std::string(#call) + ": " + cudaGetErrorString(e__); return cleanup(CTG_ERR_CUDA); } } while (0)
   const G1Affine* a_extra[3] = {(const G1Affine*)v->alpha_g1, (const G1Affine*)v->delta_g1, nullptr};
   const G1Affine* b1_extra[3] = {(const G1Affine*)v->beta_g1, nullptr, (const G1Affine*)v->delta_g1};
@@ -266,8 +294,23 @@ int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, 
   return CTG_OK;
 }
 
+void pk_free(ctg_pk* pk);
+int32_t pk_upload(ctg_ctx* ctx, const ctg_pk_view* v, uint64_t ni, uint64_t nc, int copies, int c_bits, uint64_t lo_num, uint64_t hi_num, uint64_t den, ctg_pk** out) {
+  CTG_TRY(pk_upload_impl(ctx, v, ni, nc, copies, c_bits, lo_num, hi_num, den, false, out));
+  ctg_pk* pk = *out;
+  // a whole small key with library-chosen windows also gets its batch twin (see ctg_pk::batch_twin); CTG_BATCH_TWIN=0 turns it off
+  static int twin = -1;
+  if (twin < 0) { const char* e = getenv("CTG_BATCH_TWIN"); twin = !(e && *e == '0'); }
+  if (twin && pk->shard_count == 1 && c_bits == 0 && copies == 0 && pk->log_n >= 1 && pk->log_n <= 15) {
+    const int32_t rc = pk_upload_impl(ctx, v, ni, nc, 0, 0, lo_num, hi_num, den, true, &pk->batch_twin);
+    if (rc != CTG_OK) { pk->batch_twin = nullptr; pk_free(pk); *out = nullptr; return rc; }
+  }
+  return CTG_OK;
+}
+
 void pk_free(ctg_pk* pk) {
   if (!pk) return;
+  pk_free(pk->batch_twin);
   free_bases(pk->a_ext); free_bases(pk->b1_ext); free_bases(pk->b2_ext); free_bases(pk->l); free_bases(pk->h_ext);
   delete pk;
 }
@@ -422,7 +465,7 @@ static bool same_plan(const Bases& a, const Bases& b) {
 // scratch of a lane: z_ext (m+3) | a,b,c (3n, unless the caller owns that buffer) | results: 4 G1 XYZZ + 1 G2 XYZZ | proof
 int32_t lane_bufs(ctg_ctx* ctx, ProveLane& L, uint64_t m, uint64_t n, Fr* d_abc_ext, LaneBufs* out) {
   const size_t fr_elems = m + 3 + (d_abc_ext ? 0 : 3 * n);
-  const size_t bytes = fr_elems * sizeof(Fr) + 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ) + sizeof(ctg_proof) + 256;
+  const size_t bytes = fr_elems * sizeof(Fr) + 6 * sizeof(G1XYZZ) + sizeof(G2XYZZ) + sizeof(ctg_proof) + 512;
   CTG_TRY(lane_scratch(ctx, L, bytes));
   out->d_z = (Fr*)L.scratch;
   Fr* after = out->d_z + (m + 3);
@@ -432,6 +475,7 @@ int32_t lane_bufs(ctg_ctx* ctx, ProveLane& L, uint64_t m, uint64_t n, Fr* d_abc_
   out->d_g1 = (G1XYZZ*)tail;
   out->d_g2 = (G2XYZZ*)(out->d_g1 + 4);
   out->d_proof = (ctg_proof*)(out->d_g2 + 1);
+  out->d_early = (G1XYZZ*)(((uintptr_t)(out->d_proof + 1) + 63) & ~(uintptr_t)63);   // s * A, r * B1
   return CTG_OK;
 }
 
@@ -494,6 +538,10 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
       CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr, 1, 0, sorted));
     } else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
     mark(st);                                                                 // 3,5,7,9
+    if (!host_partials_out && (j.g1_slot == 0 || j.g1_slot == 1)) {           // s * A / r * B1 under the remaining MSMs
+      scalar_mul_g1_kernel<<<1, 32, 0, st>>>(d_g1 + j.g1_slot, j.g1_slot == 0 ? s_m : r_m, B.d_early + j.g1_slot);
+      CTG_KERNEL_CHECK(ctx);
+    }
     CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
   }
   // witness map on the lane's main stream: the coset evaluations of a, b, c (the chains this rank owns) ...
@@ -527,8 +575,13 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   if (host_partials_out) {
     CTG_CUDA(ctx, cudaMemcpyAsync(host_partials_out, d_g1, 4 * sizeof(G1XYZZ) + sizeof(G2XYZZ), cudaMemcpyDeviceToHost, s0));
   } else {
-    FinalizeIn fin{d_g1 + 0, d_g1 + 1, d_g1 + 2, d_g1 + 3, d_g2, r_m, s_m};
-    finalize_kernel<<<1, 96, 0, s0>>>(fin, d_proof);
+    if (phase == 0) {
+      FinalizeSumIn fin{d_g1 + 0, B.d_early + 0, B.d_early + 1, d_g1 + 2, d_g1 + 3, d_g2};
+      finalize_sum_kernel<<<1, 96, 0, s0>>>(fin, d_proof);
+    } else {   // the MSMs of phase 1 were enqueued by another call: assemble from the sums
+      FinalizeIn fin{d_g1 + 0, d_g1 + 1, d_g1 + 2, d_g1 + 3, d_g2, r_m, s_m};
+      finalize_kernel<<<1, 96, 0, s0>>>(fin, d_proof);
+    }
     CTG_KERNEL_CHECK(ctx);
     CTG_CUDA(ctx, cudaMemcpyAsync(host_proof_out, d_proof, sizeof(ctg_proof), cudaMemcpyDeviceToHost, s0));
   }
@@ -667,10 +720,11 @@ int32_t prove_batch(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, uint32_t 
   static int fused_max_log = -1;
   if (fused_max_log < 0) { const char* e = getenv("CTG_BATCH_FUSED_MAX_LOG_N"); fused_max_log = e ? atoi(e) : 17; }
   if (r->log_n >= 1 && r->log_n <= fused_max_log && n_proofs > 1) {
-    const uint32_t chunk = batch_chunk(pk, r, n_proofs);
+    const ctg_pk* bpk = pk->batch_twin && n_proofs >= 8 ? pk->batch_twin : pk;   // the tables laid out for batches (same points, wider windows)
+    const uint32_t chunk = batch_chunk(bpk, r, n_proofs);
     for (uint32_t lo = 0; lo < n_proofs; lo += chunk) {
       const uint32_t cnt = std::min(chunk, n_proofs - lo);
-      CTG_TRY(prove_batch_fused(ctx, pk, r, cnt, z_batch + (size_t)lo * m, rs_batch + 2 * (size_t)lo, staged + lo));
+      CTG_TRY(prove_batch_fused(ctx, bpk, r, cnt, z_batch + (size_t)lo * m, rs_batch + 2 * (size_t)lo, staged + lo));
     }
     CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));
     memcpy(out, staged, need);

@@ -24,56 +24,63 @@ JUBJUB_A = R_MOD - 1
 JUBJUB_D = (-10240 * pow(10241, -1, R_MOD)) % R_MOD
 
 
+class LC:
+    """A linear combination with its value: terms = [(coefficient, variable)], variable = ("i" | "w", index); terms is None
+    when the constraint system only computes the assignment."""
+    __slots__ = ("t", "v")
+
+    def __init__(self, terms, value):
+        self.t, self.v = terms, value % R_MOD
+
+
 class ConstraintSystem:
-    """Rank-1 constraints <A, z> * <B, z> = <C, z> over z = instance ++ witness; a linear combination is a list of
-    (coefficient, variable), a variable is ("i" | "w", index).  record=False computes the assignment only (the matrices of a
-    circuit do not depend on the witness, so further witnesses of the same circuit skip the bookkeeping)."""
+    """Rank-1 constraints <A, z> * <B, z> = <C, z> over z = instance ++ witness.  record=False computes the assignment only
+    (the matrices of a circuit do not depend on the witness, so further witnesses of the same circuit skip the bookkeeping)."""
 
     def __init__(self, record=True):
         self.inst, self.wit, self.rows, self.record = [1], [], ([], [], []), record
 
     def new_input(self, v):
         self.inst.append(v % R_MOD)
-        return [(1, ("i", len(self.inst) - 1))]
+        return LC([(1, ("i", len(self.inst) - 1))] if self.record else None, v)
 
     def new_witness(self, v):
         self.wit.append(v % R_MOD)
-        return [(1, ("w", len(self.wit) - 1))]
+        return LC([(1, ("w", len(self.wit) - 1))] if self.record else None, v)
 
     def value(self, lc):
-        return sum(c * (self.inst[k] if kind == "i" else self.wit[k]) for c, (kind, k) in lc) % R_MOD
+        return lc.v
 
     def enforce(self, a, b, c):
         if self.record:
             for rows, lc in zip(self.rows, (a, b, c)):
-                rows.append(lc)
+                rows.append(lc.t)
 
     # ---- linear-combination helpers
-    @staticmethod
-    def add(a, b):
-        return a + b
+    def add(self, a, b):
+        return LC(a.t + b.t if self.record else None, a.v + b.v)
 
-    @staticmethod
-    def scale(a, k):
-        return [(c * k % R_MOD, v) for c, v in a]
+    def scale(self, a, k):
+        return LC([(c * k % R_MOD, v) for c, v in a.t] if self.record else None, a.v * k)
 
-    @classmethod
-    def sub(cls, a, b):
-        return a + cls.scale(b, R_MOD - 1)
+    def sub(self, a, b):
+        return self.add(a, self.scale(b, R_MOD - 1))
 
-    @staticmethod
-    def const(k):
-        return [(k % R_MOD, ONE)]
+    def const(self, k):
+        return LC([(k % R_MOD, ONE)] if self.record and k % R_MOD else ([] if self.record else None), k)
+
+    def zero(self):
+        return LC([] if self.record else None, 0)
 
     def mul(self, a, b):
         """A fresh witness w with a * b = w."""
-        w = self.new_witness(self.value(a) * self.value(b))
+        w = self.new_witness(a.v * b.v)
         self.enforce(a, b, w)
         return w
 
     def boolean(self, bit):
         b = self.new_witness(bit & 1)
-        self.enforce(b, self.sub(self.const(1), b), [])
+        self.enforce(b, self.sub(self.const(1), b), self.zero())
         return b
 
     def select(self, bit, if_one, if_zero):
@@ -81,14 +88,22 @@ class ConstraintSystem:
         return self.add(if_zero, self.mul(bit, self.sub(if_one, if_zero)))
 
     def enforce_equal(self, a, b):
-        self.enforce(self.sub(a, b), self.const(1), [])
+        self.enforce(self.sub(a, b), self.const(1), self.zero())
 
-    @staticmethod
-    def compact(lc):
+    def compact(self, lc):
+        if not self.record:
+            return lc
         acc = {}
-        for c, v in lc:
+        for c, v in lc.t:
             acc[v] = (acc.get(v, 0) + c) % R_MOD
-        return [(c, v) for v, c in acc.items() if c]
+        return LC([(c, v) for v, c in acc.items() if c], lc.v)
+
+    def linear(self, coeffs, lcs):
+        """sum_k coeffs[k] * lcs[k] (one row of the MDS layer)."""
+        out = self.zero()
+        for k, x in zip(coeffs, lcs):
+            out = self.add(out, self.scale(x, k))
+        return self.compact(out)
 
     # ---- export
     def r1cs(self):
@@ -97,10 +112,14 @@ class ConstraintSystem:
         out = {"num_instance": ni, "num_witness": len(self.wit), "num_constraints": len(self.rows[0])}
         for name, rows in zip("abc", self.rows):
             rp, col, val = [0], [], []
-            for lc in rows:
-                for c, (kind, k) in sorted(self.compact(lc), key=lambda t: (t[1][0] != "i", t[1][1])):
-                    col.append(k if kind == "i" else ni + k)
-                    val.append(c)
+            for terms in rows:
+                acc = {}
+                for c, v in terms:
+                    acc[v] = (acc.get(v, 0) + c) % R_MOD
+                for (kind, k), c in sorted(acc.items(), key=lambda t: (t[0][0] != "i", t[0][1])):
+                    if c:
+                        col.append(k if kind == "i" else ni + k)
+                        val.append(c)
                 rp.append(len(col))
             out[name] = {"row_ptr": np.array(rp, dtype=np.uint64), "col": np.array(col, dtype=np.uint32),
                          "val": fr_mont(val).reshape(-1, 8) if val else np.zeros((0, 8), dtype=np.uint32)}
@@ -143,19 +162,19 @@ def poseidon_permute(cs, pc, state):
     in the partial ones), MDS.  The linear layers cost no constraints; only the S-boxes do (55 * 5 = 275 for 8 + 31 rounds)."""
     half = pc.full_rounds // 2
     for r in range(pc.full_rounds + pc.partial_rounds):
-        state = [cs.compact(cs.add(s, cs.const(c))) for s, c in zip(state, pc.ark[r])]
+        state = [cs.add(s, cs.const(c)) for s, c in zip(state, pc.ark[r])]
         if r < half or r >= half + pc.partial_rounds:
             state = [_sbox(cs, s, pc.alpha) for s in state]
         else:
             state[0] = _sbox(cs, state[0], pc.alpha)
-        state = [cs.compact([t for m, s in zip(row, state) for t in cs.scale(s, m)]) for row in pc.mds]
+        state = [cs.linear(row, state) for row in pc.mds]
     return state
 
 
 def poseidon_crh(cs, pc, inputs):
     """CRH::evaluate / TwoToOneCRH::evaluate / sponge.absorb(inputs).squeeze(1) for at most two inputs (one rate block)."""
     assert 1 <= len(inputs) <= 2
-    state = [list(x) for x in inputs] + [[] for _ in range(3 - len(inputs))]
+    state = list(inputs) + [cs.zero() for _ in range(3 - len(inputs))]
     return poseidon_permute(cs, pc, state)[0]
 
 
@@ -168,8 +187,8 @@ def te_add(cs, p, q):
     t = cs.mul(cs.scale(c, JUBJUB_D), dd)
     num_x, num_y = cs.add(a, b), cs.add(dd, c)
     den_x, den_y = cs.add(cs.const(1), t), cs.sub(cs.const(1), t)
-    x3 = cs.new_witness(cs.value(num_x) * pow(cs.value(den_x), -1, R_MOD))
-    y3 = cs.new_witness(cs.value(num_y) * pow(cs.value(den_y), -1, R_MOD))
+    x3 = cs.new_witness(num_x.v * pow(den_x.v, -1, R_MOD))
+    y3 = cs.new_witness(num_y.v * pow(den_y.v, -1, R_MOD))
     cs.enforce(x3, den_x, num_x)
     cs.enforce(y3, den_y, num_y)
     return x3, y3
@@ -218,3 +237,46 @@ def sample_entries_circuit(pc, c1, leaf, leaf_sibling_hash, auth_path, leaf_inde
     dh = poseidon_crh(cs, pc, [s[0], s[1]])
     cs.enforce_equal(cs.sub(leafv, dh), sample)
     return cs
+
+
+# ---- the workload above the C ABI: encrypt -> Merkle tree -> sampled-entry statements ---------------------------------------
+JUBJUB_GEN = (8076246640662884909881801758704306714034609987455869804520522091855516602923,
+              13262374693698910701929044844600465831413122818447359594527400194675274060458)
+JUBJUB_ORDER = 6554484396890773809930967563523245729705921265872317281365359162392183254199
+
+
+def sample_entries_workload(ctx, poseidon_words, n_leaves, count, seed=1):
+    """What the seller does before proving (lib/src/seller.rs:81-127): encrypt a dataset of n_leaves byte-valued elements with
+    the device's bulk hashed ElGamal, build the Poseidon Merkle tree of the ciphertext on the device, and state `count`
+    sampled-entry proofs about it (leaf indices spread over the tree).  poseidon_words = (full, partial, alpha, mds words,
+    ark words), e.g. ctg.poseidon_reference_params().  Returns (r1cs, z (count, m, 8) Montgomery words, public inputs
+    [(sample, root)] as integers)."""
+    import random
+    from .synthetic import fr_from_mont_words, ints_to_words
+    rnd = random.Random(seed)
+    pc = PoseidonConstants.from_words(*poseidon_words)
+    pos = ctx.poseidon(*poseidon_words)
+    sk, rr = rnd.randrange(1, JUBJUB_ORDER), rnd.randrange(1, JUBJUB_ORDER)
+    msgs = [rnd.randrange(256) for _ in range(n_leaves)]
+    d_w, gen_w = fr_mont([JUBJUB_D])[0], fr_mont(list(JUBJUB_GEN))
+    pk_w = ctx.te_mul_batch(d_w, gen_w.reshape(1, 2, 8), ints_to_words([sk], 8))[0]          # keygen: pk = G * sk
+    c1_w, c2_w = ctx.elgamal_encrypt_batch(pos, d_w, gen_w, pk_w, ints_to_words([rr], 8), fr_mont(msgs).reshape(1, n_leaves, 8))
+    tree = pos.merkle_tree(c2_w[0])
+    pos.free()
+    c1 = tuple(fr_from_mont_words(c1_w[0]))
+    c2 = fr_from_mont_words(c2_w[0])
+    root = fr_from_mont_words(tree.root().reshape(1, 8))[0]
+    r1cs, zs, publics = None, [], []
+    for k in range(count):
+        idx = (k * 2654435761 + seed) % n_leaves
+        sib_w, path_w, _ = tree.generate_proof(idx)
+        sib = fr_from_mont_words(sib_w.reshape(1, 8))[0]
+        path = fr_from_mont_words(np.stack(path_w)) if path_w else []
+        cs = sample_entries_circuit(pc, c1, c2[idx], sib, path, idx, sk, msgs[idx], root, record=r1cs is None)
+        if r1cs is None:
+            r1cs = cs.r1cs()
+        zs.append(cs.assignment())
+        publics.append((msgs[idx], root))
+    m = len(zs[0])
+    z = fr_mont([v for row in zs for v in row]).reshape(count, m, 8)
+    return r1cs, z, publics

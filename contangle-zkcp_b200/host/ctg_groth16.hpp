@@ -38,6 +38,13 @@ class Context {
     int32_t rc = ctg_ctx_create(&device, 1, &ctx_);
     if (rc != CTG_OK) throw Error(rc, "ctg_ctx_create failed: no usable sm_100 CUDA device (there is no CPU fallback)");
   }
+  // several GPUs of one NVLink box in one process (ctg_ctx_create with n_devices > 1): devices[0] is the primary device; key
+  // upload, prove and the stand-alone MSMs shard over all of them by themselves, every other call runs on the primary
+  explicit Context(const std::vector<int>& devices) {
+    int32_t rc = ctg_ctx_create(devices.data(), (int)devices.size(), &ctx_);
+    if (rc != CTG_OK) throw Error(rc, "ctg_ctx_create failed: no usable sm_100 CUDA devices with peer access (there is no CPU fallback)");
+  }
+  int device_count() const { return ctg_ctx_device_count(ctx_); }
   ~Context() { ctg_ctx_destroy(ctx_); }
   Context(const Context&) = delete;
   Context& operator=(const Context&) = delete;
@@ -195,6 +202,28 @@ inline Proof create_proof(DeviceProvingKey& pk, const ConstraintSystem& cs, cons
   ctg_proof out;
   pk.ctx().check(ctg_prove(pk.ctx().raw(), pk.raw(), r1cs, z.data(), &r, &s, &out, timings));
   return Proof{out.a, out.b, out.c};
+}
+
+// Many proofs of one circuit under one key (ctg_prove_batch: one digit sort / accumulation / reduction per MSM for a chunk of
+// proofs).  systems[i] carries the i-th assignment; rs = r_0, s_0, r_1, s_1, ...
+inline std::vector<Proof> create_proofs(DeviceProvingKey& pk, const std::vector<const ConstraintSystem*>& systems, const std::vector<ctg_fr>& rs) {
+  if (systems.empty()) return {};
+  if (rs.size() != 2 * systems.size()) throw Error(CTG_ERR_INVALID, "create_proofs: two blinding scalars per proof");
+  const ctg_r1cs* r1cs = pk.r1cs_for(*systems[0]);
+  const size_t m = systems[0]->instance_assignment.size() + systems[0]->witness_assignment.size();
+  std::vector<ctg_fr> z;
+  z.reserve(m * systems.size());
+  for (const ConstraintSystem* cs : systems) {
+    if (cs->instance_assignment.size() + cs->witness_assignment.size() != m) throw Error(CTG_ERR_INVALID, "create_proofs: assignments of different circuits");
+    z.insert(z.end(), cs->instance_assignment.begin(), cs->instance_assignment.end());
+    z.insert(z.end(), cs->witness_assignment.begin(), cs->witness_assignment.end());
+  }
+  std::vector<ctg_proof> raw(systems.size());
+  pk.ctx().check(ctg_prove_batch(pk.ctx().raw(), pk.raw(), r1cs, (uint32_t)systems.size(), z.data(), rs.data(), raw.data()));
+  std::vector<Proof> out;
+  out.reserve(raw.size());
+  for (const ctg_proof& p : raw) out.push_back(Proof{p.a, p.b, p.c});
+  return out;
 }
 
 // ark_groth16::create_random_proof: `rng()` must return one uniformly random Fr as a Montgomery image, as ark-ff's

@@ -41,7 +41,7 @@ elif what == "prove":
 elif what == "batch":          # `lg` = proofs in the batch; PoE shape n_data = 1 (domain 2^13), generated key
     r1cs, zm, _ = S.poe_shape(1)
     dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
-    dpk = dp.to_device_pk()
+    dpk = dp.to_device_pk(c_bits=int(os.environ.get("CBITS", "0")))
     dp.free()
     dr = ctx.upload_r1cs(r1cs)
     zb = S.poe_shape_witnesses(ctx, 1, lg, seed=3)
