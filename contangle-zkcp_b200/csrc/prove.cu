@@ -405,15 +405,15 @@ int32_t witness_map_host(ctg_ctx* ctx, const ctg_r1cs* r, const ctg_fr* z, ctg_f
 int32_t lane_init(ctg_ctx* ctx, int idx) {
   ProveLane& L = ctx->lanes[idx];
   if (L.ready) { if (idx == 0) L.st[0] = ctx->stream; return CTG_OK; }
+  int lo_pri = 0, hi_pri = 0;
+  CTG_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));   // numerically lower = more urgent
   for (int i = 0; i < 5; i++) {
     if (idx == 0 && i == 0) { L.st[0] = ctx->stream; continue; }
-    CTG_CUDA(ctx, cudaStreamCreateWithFlags(&L.st[i], cudaStreamNonBlocking));
+    // stream 4 carries the G2 MSM: one step above the G1 MSMs, one below the witness map
+    if (i == 4 && hi_pri + 1 < lo_pri) CTG_CUDA(ctx, cudaStreamCreateWithPriority(&L.st[i], cudaStreamNonBlocking, hi_pri + 1));
+    else CTG_CUDA(ctx, cudaStreamCreateWithFlags(&L.st[i], cudaStreamNonBlocking));
   }
-  {
-    int lo_pri = 0, hi_pri = 0;
-    CTG_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
-    CTG_CUDA(ctx, cudaStreamCreateWithPriority(&L.st_hi, cudaStreamNonBlocking, hi_pri));
-  }
+  CTG_CUDA(ctx, cudaStreamCreateWithPriority(&L.st_hi, cudaStreamNonBlocking, hi_pri));
   CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_z, cudaEventDisableTiming));
   CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_zfull, cudaEventDisableTiming));
   CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_wm, cudaEventDisableTiming));
@@ -527,7 +527,13 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
                        {2, &pk->a_ext, d_z + pk->ext_lo, pk->ext_cnt, 0},
                        {3, &pk->b1_ext, d_z + pk->ext_lo, pk->ext_cnt, 1},
                        {4, &pk->b2_ext, d_z + pk->ext_lo, pk->ext_cnt, -1}};
-  for (const Job& j : jobs) {
+  // The G2 MSM goes first, on a stream of raised priority: it is the longest of the four and ends in the longest latency-bound
+  // tail (bucket reduction over Fq2, ~6 ms at 2^20); queued first, its tail runs UNDER the accumulate kernels of the G1 MSMs
+  // instead of after them.  (Timing events keep their slots: 2 + 2 * index in `jobs`.)
+  const int order[4] = {3, 1, 2, 0};
+  for (int oi = 0; oi < 4; oi++) {
+    const Job& j = jobs[order[oi]];
+    ne = 2 + 2 * order[oi];
     cudaStream_t st = L.st[j.stream];
     CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
     mark(st);                                                                 // 2,4,6,8
@@ -544,6 +550,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
     }
     CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
   }
+  ne = 10;
   // witness map on the lane's main stream: the coset evaluations of a, b, c (the chains this rank owns) ...
   if (phase != 1 || chain_mask != 0) {   // tables are built (and synchronised) before any chain is enqueued
     NttDomain* dom;
@@ -665,7 +672,8 @@ static int32_t prove_batch_fused(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs*
   struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
   const Job jobs[4] = {{1, &pk->l, d_z + pk->ni, pk->l_cnt, 2}, {2, &pk->a_ext, d_z, pk->ext_cnt, 0}, {3, &pk->b1_ext, d_z, pk->ext_cnt, 1}, {4, &pk->b2_ext, d_z, pk->ext_cnt, -1}};
   const bool share = same_plan(pk->a_ext, pk->b1_ext) && pk->ext_cnt > 0;
-  for (const Job& j : jobs) {
+  for (int oi : {3, 1, 2, 0}) {   // the G2 MSM first (see prove_enqueue)
+    const Job& j = jobs[oi];
     cudaStream_t st = L.st[j.stream];
     CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
     if (j.g1_slot >= 0) {
