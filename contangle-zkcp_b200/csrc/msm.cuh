@@ -428,7 +428,7 @@ template <class F, int CH> __global__ void __launch_bounds__(128) progression_ke
     if (!acc.is_inf()) run = run * (acc.ZZ * acc.ZZZ);
     acc = xyzz_madd(acc, step);
   }
-  F inv = run.inv();
+  F inv = run.inv_bingcd();
 #pragma unroll 1
   for (int j = CH - 1; j >= 0; j--) {
     if (i0 + j >= n) { if (!pts[j].is_inf()) inv = inv * (pts[j].ZZ * pts[j].ZZZ); continue; }
@@ -460,7 +460,7 @@ template <class F, int MAXC> __global__ void __launch_bounds__(128) precompute_k
     prod[j] = run;
     if (!cur.is_inf()) run = run * (cur.ZZ * cur.ZZZ);
   }
-  F inv = run.inv();
+  F inv = run.inv_bingcd();
 #pragma unroll 1
   for (int j = copies - 1; j >= 1; j--) {
     Affine<F> o = Affine<F>::inf();

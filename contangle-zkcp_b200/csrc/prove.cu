@@ -409,9 +409,7 @@ int32_t lane_init(ctg_ctx* ctx, int idx) {
   CTG_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));   // numerically lower = more urgent
   for (int i = 0; i < 5; i++) {
     if (idx == 0 && i == 0) { L.st[0] = ctx->stream; continue; }
-    // stream 4 carries the G2 MSM: one step above the G1 MSMs, one below the witness map
-    if (i == 4 && hi_pri + 1 < lo_pri) CTG_CUDA(ctx, cudaStreamCreateWithPriority(&L.st[i], cudaStreamNonBlocking, hi_pri + 1));
-    else CTG_CUDA(ctx, cudaStreamCreateWithFlags(&L.st[i], cudaStreamNonBlocking));
+    CTG_CUDA(ctx, cudaStreamCreateWithFlags(&L.st[i], cudaStreamNonBlocking));
   }
   CTG_CUDA(ctx, cudaStreamCreateWithPriority(&L.st_hi, cudaStreamNonBlocking, hi_pri));
   CTG_CUDA(ctx, cudaEventCreateWithFlags(&L.ev_z, cudaEventDisableTiming));
@@ -485,7 +483,8 @@ int32_t lane_bufs(ctg_ctx* ctx, ProveLane& L, uint64_t m, uint64_t n, Fr* d_abc_
 static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const ctg_r1cs* r, const ctg_fr* z, const Fr& r_m, const Fr& s_m,
                              ctg_proof* host_proof_out, void* host_partials_out, bool timed,
                              int phase = 0 /* 0 = whole proof, 1 = up to the coset evaluations, 2 = the rest */, uint32_t chain_mask = 7,
-                             Fr* d_abc_ext = nullptr /* caller-owned 3n buffer for the a, b, c chains (multi-GPU exchange) */) {
+                             Fr* d_abc_ext = nullptr /* caller-owned 3n buffer for the a, b, c chains (multi-GPU exchange) */,
+                             bool early_mul = true /* s * A and r * B1 on the streams of their MSMs (not for the partial-sum ABI) */) {
   CTG_TRY(lane_init(ctx, lane_idx));
   ProveLane& L = ctx->lanes[lane_idx];
   const uint64_t n = r->n, m = pk->m;
@@ -527,10 +526,10 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
                        {2, &pk->a_ext, d_z + pk->ext_lo, pk->ext_cnt, 0},
                        {3, &pk->b1_ext, d_z + pk->ext_lo, pk->ext_cnt, 1},
                        {4, &pk->b2_ext, d_z + pk->ext_lo, pk->ext_cnt, -1}};
-  // The G2 MSM goes first, on a stream of raised priority: it is the longest of the four and ends in the longest latency-bound
-  // tail (bucket reduction over Fq2, ~6 ms at 2^20); queued first, its tail runs UNDER the accumulate kernels of the G1 MSMs
-  // instead of after them.  (Timing events keep their slots: 2 + 2 * index in `jobs`.)
-  const int order[4] = {3, 1, 2, 0};
+  // Queue order = L, A, B1, B2.  (Queueing the G2 MSM first on a raised-priority stream, so that its latency-bound tail runs under
+  // the G1 accumulate kernels, was measured: 2^16 7.8 -> 7.5 ms, but 2^22 154 -> 159 ms and the fused batch 2 045 -> 1 441 proofs/s:
+  // the G2 kernels then delay the sorts of the other MSMs.  Timing events keep their slots: 2 + 2 * index in `jobs`.)
+  const int order[4] = {0, 1, 2, 3};
   for (int oi = 0; oi < 4; oi++) {
     const Job& j = jobs[order[oi]];
     ne = 2 + 2 * order[oi];
@@ -544,7 +543,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
       CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr, 1, 0, sorted));
     } else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
     mark(st);                                                                 // 3,5,7,9
-    if (!host_partials_out && (j.g1_slot == 0 || j.g1_slot == 1)) {           // s * A / r * B1 under the remaining MSMs
+    if (early_mul && !host_partials_out && (j.g1_slot == 0 || j.g1_slot == 1)) {   // s * A / r * B1 under the remaining MSMs
       scalar_mul_g1_kernel<<<1, 32, 0, st>>>(d_g1 + j.g1_slot, j.g1_slot == 0 ? s_m : r_m, B.d_early + j.g1_slot);
       CTG_KERNEL_CHECK(ctx);
     }
@@ -672,7 +671,7 @@ static int32_t prove_batch_fused(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs*
   struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
   const Job jobs[4] = {{1, &pk->l, d_z + pk->ni, pk->l_cnt, 2}, {2, &pk->a_ext, d_z, pk->ext_cnt, 0}, {3, &pk->b1_ext, d_z, pk->ext_cnt, 1}, {4, &pk->b2_ext, d_z, pk->ext_cnt, -1}};
   const bool share = same_plan(pk->a_ext, pk->b1_ext) && pk->ext_cnt > 0;
-  for (int oi : {3, 1, 2, 0}) {   // the G2 MSM first (see prove_enqueue)
+  for (int oi : {0, 1, 2, 3}) {
     const Job& j = jobs[oi];
     cudaStream_t st = L.st[j.stream];
     CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
@@ -773,7 +772,7 @@ int32_t prove_partial_begin(ctg_ctx* ctx, const ctg_pk* pk, const ctg_r1cs* r, c
   Fr r_m, s_m;
   memcpy(&r_m, rr, sizeof(Fr));
   memcpy(&s_m, ss, sizeof(Fr));
-  CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, nullptr, nullptr, false, 1, chain_mask, (Fr*)d_abc));
+  CTG_TRY(prove_enqueue(ctx, 0, pk, r, z, r_m, s_m, nullptr, nullptr, false, 1, chain_mask, (Fr*)d_abc, false));
   CTG_CUDA(ctx, cudaStreamSynchronize(ctx->lanes[0].st[0]));   // the chains are complete: safe to hand to a collective on any stream
   return CTG_OK;
 }
@@ -854,6 +853,43 @@ int32_t prove_group_b(Group* g, const ctg_r1cs* r0, const Fr& r_m, const Fr& s_m
   CTG_CUDA(ctx, cudaEventRecord(g->ev_h, sw));
   return CTG_OK;
 }
+// slots of a device's partial record: [0] = A_d, [1] = B1_d -> C_d, [2] = L_d, [3] = H_d (G1 XYZZ), then B2_d (G2 XYZZ)
+__global__ void __launch_bounds__(32) group_share_kernel(const G1XYZZ* early /* s A_d, r B1_d */, G1XYZZ* g1) {
+  if (threadIdx.x != 0) return;
+  G1XYZZ c = xyzz_add(early[0], early[1]);
+  c = xyzz_add(c, g1[2]);
+  c = xyzz_add(c, g1[3]);
+  g1[1] = c;
+}
+// device 0: A = sum_d A_d, C = sum_d C_d, B = sum_d B2_d by pairwise trees (three warps, up to 8 shards), then to affine
+template <class P> __device__ __forceinline__ P shard_tree_sum(const char* parts, size_t offset, uint32_t k, P* sh, unsigned lane) {
+  auto part = [&](uint32_t i) { return i < k ? *reinterpret_cast<const P*>(parts + (size_t)i * kPartialBytes + offset) : P::inf(); };
+  if (lane < 4) sh[lane] = xyzz_add(part(lane), part(lane + 4));
+  __syncwarp();
+  if (lane < 2) sh[lane] = xyzz_add(sh[lane], sh[lane + 2]);
+  __syncwarp();
+  P total = P::inf();
+  if (lane == 0) total = xyzz_add(sh[0], sh[1]);
+  return total;
+}
+__global__ void __launch_bounds__(96) group_finalize_kernel(const char* parts, uint32_t k, ctg_proof* out) {
+  __shared__ G1XYZZ sh1[2][4];
+  __shared__ G2XYZZ sh2[4];
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < 2) {
+    G1XYZZ t = shard_tree_sum<G1XYZZ>(parts, warp * sizeof(G1XYZZ), k, sh1[warp], lane);
+    if (lane == 0) {
+      G1Affine a = xyzz_to_affine(t);
+      *reinterpret_cast<G1Affine*>(warp == 0 ? (void*)&out->a : (void*)&out->c) = a;
+    }
+  } else {
+    G2XYZZ t = shard_tree_sum<G2XYZZ>(parts, 4 * sizeof(G1XYZZ), k, sh2, lane);
+    if (lane == 0) {
+      G2Affine b = xyzz_to_affine(t);
+      *reinterpret_cast<G2Affine*>(&out->b) = b;
+    }
+  }
+}
 int32_t prove_group_c(Group* g, int d, const ctg_pk* pk, const ctg_r1cs* r) {
   ctg_ctx* ctx = g->ctx[d];
   ProveLane& L = ctx->lanes[0];
@@ -871,6 +907,10 @@ int32_t prove_group_c(Group* g, int d, const ctg_pk* pk, const ctg_r1cs* r) {
   CTG_CUDA(ctx, cudaEventRecord(L.ev_wm, sw));
   CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_wm, 0));
   for (int i = 1; i < 5; i++) CTG_CUDA(ctx, cudaStreamWaitEvent(s0, L.ev_done[i], 0));
+  // C is linear in the shards: C = sum_d (s A_d + r B1_d + L_d + H_d).  s A_d and r B1_d were started by phase A on the streams of
+  // their MSMs (prove_enqueue early_mul), so each device closes ITS share here and device 0 only adds points.
+  group_share_kernel<<<1, 32, 0, s0>>>(B.d_early, B.d_g1);
+  CTG_KERNEL_CHECK(ctx);
   CTG_CUDA(ctx, cudaMemcpyPeerAsync((char*)g->d_parts0 + (size_t)d * kPartialBytes, g->ctx[0]->device, B.d_g1, ctx->device, kPartialBytes, s0));
   CTG_CUDA(ctx, cudaEventRecord(g->ev_part[d], s0));
   return CTG_OK;
@@ -897,10 +937,8 @@ int32_t prove_group_d(Group* g, const Fr& r_m, const Fr& s_m, ctg_proof* out) {
   G1XYZZ* d_s1 = (G1XYZZ*)(base + (size_t)g->n * kPartialBytes);
   G2XYZZ* d_s2 = (G2XYZZ*)(d_s1 + 4);
   ctg_proof* d_proof = (ctg_proof*)(d_s2 + 1);
-  combine_partials_packed_kernel<<<1, 160, 0, s0>>>(base, (uint32_t)g->n, d_s1, d_s2);
-  CTG_KERNEL_CHECK(ctx);
-  FinalizeIn fin{d_s1 + 0, d_s1 + 1, d_s1 + 2, d_s1 + 3, d_s2, r_m, s_m};
-  finalize_kernel<<<1, 96, 0, s0>>>(fin, d_proof);
+  (void)r_m; (void)s_m;   // already inside every device's C_d
+  group_finalize_kernel<<<1, 96, 0, s0>>>(base, (uint32_t)g->n, d_proof);
   CTG_KERNEL_CHECK(ctx);
   CTG_CUDA(ctx, cudaMemcpyAsync(g->h_proof, d_proof, sizeof(ctg_proof), cudaMemcpyDeviceToHost, s0));
   CTG_CUDA(ctx, cudaStreamSynchronize(s0));

@@ -1,0 +1,12 @@
+O=gpurun_out; T=r2q
+mkdir -p $O
+(time timeout 1500 python -m pytest tests -m gpu -x -q --timeout 300) > $O/${T}_pytest.log 2>&1; echo "pytest exit $?"; tail -4 $O/${T}_pytest.log
+(time timeout 1500 python bench.py) > $O/${T}_bench.json 2> $O/${T}_bench.err; echo "bench exit $?"; tail -5 $O/${T}_bench.err; python - <<'PY'
+import json
+l=json.load(open('gpurun_out/r2q_bench.json'))
+ex=l.pop('extra',{})
+print(json.dumps(l)[:300])
+for k,v in ex.items():
+    if k.startswith('batched'): print(k, json.dumps(v)[:500])
+    elif k.startswith('groth16'): print(k, v.get('wall_ms_median'), v.get('wall_ms_median_pageable_z'), v.get('cpu_port_prove_ms'), v.get('gpu_matches_cpu'), json.dumps(v.get('stages_ms'))[:400])
+PY
