@@ -249,10 +249,10 @@ __device__ __forceinline__ uint64_t tw_pos(const TileGeom& g, uint32_t w) {
 
 // One round of K butterfly levels on register-resident groups of 2^K elements spaced 2^g apart in the tile.
 // DIF: levels run from log_h = log_h0 down; DIT: from log_h0 up.  `tile` elements, all threads of the CTA take part.
-template <int K, bool DIT>
+template <int K, bool DIT, int THREADS>
 __device__ __forceinline__ void ntt_round(unsigned char* sm, const NttPass& p, const TileGeom& geo, int g, int log_h0, int tile) {
   constexpr int R = 1 << K;
-  for (uint32_t grp = threadIdx.x; grp < (uint32_t)(tile >> K); grp += kThreads) {
+  for (uint32_t grp = threadIdx.x; grp < (uint32_t)(tile >> K); grp += THREADS) {
     const uint32_t low = grp & ((1u << g) - 1);
     const uint32_t i0 = ((grp >> g) << (g + K)) | low;
     Fr x[R];
@@ -287,10 +287,14 @@ __device__ __forceinline__ void ntt_round(unsigned char* sm, const NttPass& p, c
   }
 }
 
-// MAXK = 3: radix-8 rounds, 128 registers, two CTAs per SM (16 warps).  MAXK = 2: radix-4 rounds, 80 registers, three CTAs per SM
-// (24 warps): one more shared-memory exchange per pass for half as many live registers.  CTG_NTT_RADIX4=1 selects the latter.
-template <int MAXK>
-__global__ void __launch_bounds__(kThreads, MAXK == 3 ? 2 : 3) ntt_pass_tma_kernel(const __grid_constant__ CUtensorMap tmap, NttPass p) {
+// Instantiations.  <3, 128> (default): radix-8 rounds, 128 registers, tiles of 2^10 elements (32 KB), 128 threads -- a CTA is
+// 16 K registers + 33 KB, so four are resident per SM alone (16 warps) AND one still fits beside two bucket-accumulation CTAs
+// of a concurrent MSM (2 x 23.5 K registers): inside a proof the witness map runs on a high-priority stream while the MSM
+// kernels hold the SMs, and a 32 K-register CTA would have to wait for one of those long-lived CTAs to retire (measured: the
+// 2^22 proof took 169-175 ms with <3, 256> against 162 ms with the 58-register round-1 kernel).  <3, 256>: the same with
+// tiles of 2^11 (CTG_NTT_TILE=11).  <2, 256>: radix-4 rounds, 80 registers, three CTAs per SM (CTG_NTT_RADIX4=1) -- an A/B arm.
+template <int MAXK, int THREADS>
+__global__ void __launch_bounds__(THREADS, THREADS == 128 ? 4 : (MAXK == 3 ? 2 : 3)) ntt_pass_tma_kernel(const __grid_constant__ CUtensorMap tmap, NttPass p) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mbar;
   unsigned char* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // the swizzle pattern is a function of address bits 7..9
@@ -331,7 +335,7 @@ __global__ void __launch_bounds__(kThreads, MAXK == 3 ? 2 : 3) ntt_pass_tma_kern
     return geo.strided ? base + ((uint64_t)(e >> geo.log_C) << geo.log_cpb) + (e & ((1u << geo.log_C) - 1)) : base + e;
   };
   if (p.pre_tab) {
-    for (uint32_t e = threadIdx.x; e < (uint32_t)tile; e += kThreads) {
+    for (uint32_t e = threadIdx.x; e < (uint32_t)tile; e += THREADS) {
       const uint64_t a = addr_of(e);
       sts_fr(sm, e, lds_fr(sm, e) * ldg_fr(p.pre_tab + (p.pre_bitrev ? bitrev_idx(a, p.log_n) : a)));
     }
@@ -348,20 +352,20 @@ __global__ void __launch_bounds__(kThreads, MAXK == 3 ? 2 : 3) ntt_pass_tma_kern
     const int log_h0 = p.dit ? t : p.S - 1 - t;
     const int g = dbase + (p.dit ? log_h0 : log_h0 - (K - 1));
     if (p.dit) {
-      if (MAXK == 3 && K == 3) ntt_round<MAXK, true>(sm, p, geo, g, log_h0, tile);
-      else if (K == 2) ntt_round<2, true>(sm, p, geo, g, log_h0, tile);
-      else ntt_round<1, true>(sm, p, geo, g, log_h0, tile);
+      if (MAXK == 3 && K == 3) ntt_round<MAXK, true, THREADS>(sm, p, geo, g, log_h0, tile);
+      else if (K == 2) ntt_round<2, true, THREADS>(sm, p, geo, g, log_h0, tile);
+      else ntt_round<1, true, THREADS>(sm, p, geo, g, log_h0, tile);
     } else {
-      if (MAXK == 3 && K == 3) ntt_round<MAXK, false>(sm, p, geo, g, log_h0, tile);
-      else if (K == 2) ntt_round<2, false>(sm, p, geo, g, log_h0, tile);
-      else ntt_round<1, false>(sm, p, geo, g, log_h0, tile);
+      if (MAXK == 3 && K == 3) ntt_round<MAXK, false, THREADS>(sm, p, geo, g, log_h0, tile);
+      else if (K == 2) ntt_round<2, false, THREADS>(sm, p, geo, g, log_h0, tile);
+      else ntt_round<1, false, THREADS>(sm, p, geo, g, log_h0, tile);
     }
     t += K;
     __syncthreads();
   }
 
   if (p.post_tab || p.post_const) {
-    for (uint32_t e = threadIdx.x; e < (uint32_t)tile; e += kThreads) {
+    for (uint32_t e = threadIdx.x; e < (uint32_t)tile; e += THREADS) {
       Fr v = lds_fr(sm, e);
       if (p.post_tab) {
         const uint64_t a = addr_of(e);
@@ -492,8 +496,9 @@ int32_t ntt_get_domain(ctg_ctx* ctx, int log_n, NttDomain** out) {
   if (ctx->domains.empty())
   {
     CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32));
-    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
-    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<3, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << 10) * 32 + 1024));
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<3, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
+    CTG_CUDA(ctx, cudaFuncSetAttribute(ntt_pass_tma_kernel<2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kTileLog) * 32 + 1024));
   }
   CTG_CUDA(ctx, cudaStreamSynchronize(st));  // other streams (prover lanes) may use the tables next
   ctx->domains[log_n] = d;
@@ -524,6 +529,11 @@ static bool ntt_radix4() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("CTG_NTT_RADIX4"); v = e && *e == '1'; }
   return v != 0;
+}
+static int ntt_tma_tile_log() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CTG_NTT_TILE"); v = e && atoi(e) == 11 ? 11 : 10; }
+  return v;
 }
 static bool ntt_legacy() {
   static int v = -1;
@@ -559,10 +569,10 @@ static int32_t make_tile_map(ctg_ctx* ctx, CUtensorMap* tm, Fr* d, const NttPass
 
 struct PassGeom { int log_blk, S; };
 // DIF order (large sub-transforms first).  DIT uses the same list reversed.
-static std::vector<PassGeom> plan_passes(int log_n) {
+static std::vector<PassGeom> plan_passes(int log_n, int tile_log) {
   std::vector<PassGeom> v;
   int rem = log_n;
-  while (rem > kTileLog) { v.push_back({rem, kStridedLevels}); rem -= kStridedLevels; }
+  while (rem > tile_log) { v.push_back({rem, kStridedLevels}); rem -= kStridedLevels; }
   if (rem > 0) v.push_back({rem, rem});
   return v;
 }
@@ -575,7 +585,15 @@ struct Fuse {
 
 // Runs all passes of one transform.  dit = 0: natural -> bit-reversed; dit = 1: the reverse.
 static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit, const Fuse& f, cudaStream_t st, uint32_t batch = 1) {
-  std::vector<PassGeom> plan = plan_passes(log_n);
+  // kernel and tile size first: the pass structure depends on the tile
+  const bool aligned = (reinterpret_cast<uintptr_t>(d) & 15) == 0;
+  int tile_log = kTileLog;
+  bool use_tma = false;
+  if (!ntt_legacy() && aligned) {
+    const int t = ntt_radix4() ? kTileLog : ntt_tma_tile_log();
+    if ((log_n < t ? log_n : t) >= kTmaMinLogTile) { use_tma = true; tile_log = t; }
+  }
+  std::vector<PassGeom> plan = plan_passes(log_n, tile_log);
   if (dit) std::reverse(plan.begin(), plan.end());
   const uint64_t n = 1ull << log_n;
   if (plan.empty()) {  // n == 1: only the scale factors act
@@ -590,7 +608,7 @@ static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit,
     p.log_n = log_n;
     p.log_blk = plan[i].log_blk;
     p.S = plan[i].S;
-    p.log_tile = log_n < kTileLog ? log_n : kTileLog;
+    p.log_tile = log_n < tile_log ? log_n : tile_log;
     p.dit = dit;
     p.tw = tw;
     const bool first = i == 0, last = i + 1 == plan.size();
@@ -602,11 +620,12 @@ static int32_t run_passes(ctg_ctx* ctx, Fr* d, int log_n, const Fr* tw, int dit,
     p.post_c = f.post_c;
     unsigned blocks = (unsigned)(n >> p.log_tile);
     size_t smem = ((size_t)1 << p.log_tile) * 32;
-    if (p.log_tile >= kTmaMinLogTile && !ntt_legacy() && (reinterpret_cast<uintptr_t>(d) & 15) == 0) {
+    if (use_tma) {
       CUtensorMap tm;
       CTG_TRY(make_tile_map(ctx, &tm, d, p, batch));
-      if (ntt_radix4()) ntt_pass_tma_kernel<2><<<dim3(blocks, batch), kThreads, smem + 1024, st>>>(tm, p);
-      else ntt_pass_tma_kernel<3><<<dim3(blocks, batch), kThreads, smem + 1024, st>>>(tm, p);
+      if (ntt_radix4()) ntt_pass_tma_kernel<2, 256><<<dim3(blocks, batch), 256, smem + 1024, st>>>(tm, p);
+      else if (tile_log == 10) ntt_pass_tma_kernel<3, 128><<<dim3(blocks, batch), 128, smem + 1024, st>>>(tm, p);
+      else ntt_pass_tma_kernel<3, 256><<<dim3(blocks, batch), 256, smem + 1024, st>>>(tm, p);
     } else {
       ntt_pass_kernel<<<dim3(blocks, batch), kThreads, smem, st>>>(d, p);
     }
