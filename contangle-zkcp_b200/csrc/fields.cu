@@ -18,6 +18,26 @@ template <class F> __global__ void __launch_bounds__(128) field_inv_kernel(const
   out[i] = a[i].inv_bingcd();
 }
 
+// The lane-paired Fq2 arithmetic of the G2 bucket-reduction tail (msm_pair.cuh), element-wise, for the test-suite:
+//   which = 0: a * b     1: a^2     2: a * b - b * a^2  (Fq2L::mul2_sub(a, b, b, a^2))     3: (a == 0) ? 1 : 0 in c0 (is_zero agreement)
+}  // namespace ctg
+#include "msm.cuh"   // msm_pair.cuh needs copy16 / HalveArgs
+namespace ctg {
+__global__ void __launch_bounds__(128) fq2_paired_op_kernel(const Fq2* __restrict__ a, const Fq2* __restrict__ b, Fq2* __restrict__ out, size_t n, int which) {
+  const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t i = gt >> 1;
+  const unsigned par = (unsigned)(gt & 1);
+  if (i >= n) return;   // pairs leave together
+  const Fq* fa = reinterpret_cast<const Fq*>(a + i);
+  const Fq* fb = reinterpret_cast<const Fq*>(b + i);
+  Fq2L x{fa[par]}, y{fb[par]}, r;
+  if (which == 0) r = x * y;
+  else if (which == 1) r = x.sqr();
+  else if (which == 2) r = Fq2L::mul2_sub(x, y, y, x.sqr());
+  else { const bool z = x.is_zero(); r = z ? Fq2L::one() : Fq2L::zero(); }
+  reinterpret_cast<Fq*>(out + i)[par] = r.v;
+}
+
 template <class F> static int32_t launch_op(ctg_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n, cudaStream_t st) {
   unsigned blocks = (unsigned)((n + 127) / 128);
   const F* pa = (const F*)a; const F* pb = (const F*)b; F* po = (F*)out;
@@ -37,7 +57,13 @@ int32_t field_op_dev(ctg_ctx* ctx, int field, int op, const void* a, const void*
   switch (field) {
     case CTG_FIELD_FR: return launch_op<Fr>(ctx, op, a, b, out, n, st);
     case CTG_FIELD_FQ: return launch_op<Fq>(ctx, op, a, b, out, n, st);
-    case CTG_FIELD_FQ2: return launch_op<Fq2>(ctx, op, a, b, out, n, st);
+    case CTG_FIELD_FQ2:
+      if (op >= CTG_OP_PAIRED_MUL && op <= CTG_OP_PAIRED_IS_ZERO) {
+        fq2_paired_op_kernel<<<(unsigned)((2 * n + 127) / 128), 128, 0, st>>>((const Fq2*)a, (const Fq2*)b, (Fq2*)out, n, op - CTG_OP_PAIRED_MUL);
+        CTG_KERNEL_CHECK(ctx);
+        return CTG_OK;
+      }
+      return launch_op<Fq2>(ctx, op, a, b, out, n, st);
   }
   return fail(ctx, CTG_ERR_INVALID, "field op: unknown field");
 }

@@ -18,6 +18,8 @@
 // so only G = ceil(W / copies) bucket sets exist; with copies = W there is a single set and no
 // doubling chain at the end.
 #pragma once
+#include <type_traits>
+#include <cstdlib>
 #include "ctg_internal.h"
 #include <cstdlib>
 
@@ -360,6 +362,15 @@ template <class F> __global__ void __launch_bounds__(32) msm_reduce_final_kernel
   if (lane == 0) copy16(set_out[blockIdx.x], acc);
 }
 
+}  // namespace ctg
+#include "msm_pair.cuh"   // lane-paired G2 versions of the two latency-bound kernels above
+namespace ctg {
+inline bool g2_pair_reduce() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CTG_G2_PAIR"); v = !(e && *e == '0'); }
+  return v != 0;
+}
+
 // ---- 7. window combine --------------------------------------------------------------------------
 // sum_g 2^(c g) S_g, single thread (G - 1) * c doublings; G = 1 when every window is precomputed
 template <class F> __global__ void msm_horner_kernel(const XYZZ<F>* sets, int nsets, int c, XYZZ<F>* out, uint32_t batch) {
@@ -695,12 +706,22 @@ template <class F> struct MsmHost {
           }
         }
         if ((used + 64) * sizeof(XYZZ<F>) > ws.cap_chunk_bytes) return fail(ctx, CTG_ERR_STATE, "msm: reduction scratch too small");
-        msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
+        if constexpr (std::is_same<F, Fq2>::value) {
+          if (g2_pair_reduce()) msm_halve_pair_kernel<0><<<dim3((2 * threads + 127) / 128, nsets), 128, 0, st>>>(args);
+          else msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
+        } else {
+          msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
+        }
         CTG_KERNEL_CHECK(ctx);
         trees.swap(next);
       }
       XYZZ<F>* set_out = plan.nsets == 1 ? d_out : take(1);
-      msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
+      if constexpr (std::is_same<F, Fq2>::value) {
+        if (g2_pair_reduce()) msm_reduce_final_pair_kernel<0><<<nsets, 64, 0, st>>>(finals, nslots, 2, shift, set_out);
+        else msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
+      } else {
+        msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
+      }
       CTG_KERNEL_CHECK(ctx);
       if (plan.nsets > 1) {
         msm_horner_kernel<F><<<(batch + 31) / 32, 32, 0, st>>>(set_out, plan.nsets, plan.c, d_out, batch);

@@ -22,6 +22,7 @@ PARTIAL_W = 4 * 2 * G1_W + 2 * G2_W   # ctg_proof_partial: 4 G1 XYZZ + 1 G2 XYZZ
 SCALARS_CANONICAL, SCALARS_MONT, MSM_TIMED = 0, 1, 0x100
 FIELD_FR, FIELD_FQ, FIELD_FQ2 = 0, 1, 2
 OP_MUL, OP_ADD, OP_SUB, OP_INV = 0, 1, 2, 3
+OP_PAIRED_MUL, OP_PAIRED_SQR, OP_PAIRED_MUL2SUB, OP_PAIRED_IS_ZERO = 4, 5, 6, 7   # FIELD_FQ2 only: the lane-paired arithmetic of csrc/msm_pair.cuh
 
 # every symbol include/ctg_groth16.h declares (checked by tests/test_abi_cpu.py)
 EXPORTS = [

@@ -151,6 +151,12 @@ int32_t ctg_host_free(ctg_ctx* ctx, void* h_ptr);
 #define CTG_OP_ADD 1
 #define CTG_OP_SUB 2
 #define CTG_OP_INV 3 /* out[i] = a[i]^-1 (b ignored, may equal a); 0 -> 0.  The binary-GCD inversion the batched-affine MSM uses */
+/* CTG_FIELD_FQ2 only -- the lane-paired Fq2 arithmetic of the G2 bucket-reduction tail (one component per lane of a lane pair),
+ * exposed so that it can be checked element by element: a * b, a^2, a * b - b * a^2, and [a == 0] (as the element 1 or 0) */
+#define CTG_OP_PAIRED_MUL 4
+#define CTG_OP_PAIRED_SQR 5
+#define CTG_OP_PAIRED_MUL2SUB 6
+#define CTG_OP_PAIRED_IS_ZERO 7
 /* out[i] = a[i] (op) b[i]; host buffers of n elements (32 / 48 / 96 bytes each) */
 int32_t ctg_field_op_batch(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n);
 int32_t ctg_fr_mul_batch(ctg_ctx* ctx, const ctg_fr* a, const ctg_fr* b, ctg_fr* out, size_t n);

@@ -62,6 +62,30 @@ def test_fq2_mul(ctx):
     assert np.array_equal(ctx.field_op(ctg.FIELD_FQ2, ctg.OP_MUL, a, b), ark.fq2_mul(a, b))
 
 
+def test_fq2_lane_paired_arithmetic(ctx):
+    """csrc/msm_pair.cuh: an Fq2 element on an even / odd lane pair (the G2 bucket-reduction tail).  Products, squares, the fused
+    a b - c d and the pair's agreement on is_zero, element by element against the oracle -- with operands whose components are
+    0, 1, p - 1 or random, an odd element count (a warp with an idle tail) and every zero / non-zero mix of the two components."""
+    edge = [0, 1, B.P_MOD - 1, 2, (B.P_MOD - 1) // 2]
+    vals = [(x, y) for x in edge for y in edge] + [(rnd.randrange(B.P_MOD), rnd.randrange(B.P_MOD)) for _ in range(2974)]
+    vals2 = vals[::-1]
+    n = len(vals)
+    assert n % 2 == 1
+    a = ark.ints_to_words([c for v in vals for c in v], 12).reshape(n, 24)
+    b = ark.ints_to_words([c for v in vals2 for c in v], 12).reshape(n, 24)
+    ab = ark.fq2_mul(a, b)
+    aa = ark.fq2_mul(a, a)
+    assert np.array_equal(ctx.field_op(ctg.FIELD_FQ2, ctg.OP_PAIRED_MUL, a, b), ab)
+    assert np.array_equal(ctx.field_op(ctg.FIELD_FQ2, ctg.OP_PAIRED_SQR, a, b), aa)
+    baa = ark.fq2_mul(b, aa)
+    want = ark.fq_sub(ab.reshape(2 * n, 12), baa.reshape(2 * n, 12)).reshape(n, 24)      # component-wise in the oracle
+    assert np.array_equal(ctx.field_op(ctg.FIELD_FQ2, ctg.OP_PAIRED_MUL2SUB, a, b), want)
+    isz = ctx.field_op(ctg.FIELD_FQ2, ctg.OP_PAIRED_IS_ZERO, a, b)
+    one = ark.ints_to_words([B.FQ_R % B.P_MOD if hasattr(B, "FQ_R") else pow(2, 384, B.P_MOD), 0], 12).reshape(24)
+    for i, (x, y) in enumerate(vals):
+        assert np.array_equal(isz[i], one if (x == 0 and y == 0) else np.zeros(24, dtype=np.uint32)), (i, x == 0, y == 0)
+
+
 def test_empty_inputs(ctx):
     e = np.zeros((0, 8), dtype=np.uint32)
     assert ctx.field_op(ctg.FIELD_FR, ctg.OP_MUL, e, e).shape == (0, 8)
