@@ -365,6 +365,14 @@ template <class F> __global__ void __launch_bounds__(32) msm_reduce_final_kernel
 }  // namespace ctg
 #include "msm_pair.cuh"   // lane-paired G2 versions of the two latency-bound kernels above
 namespace ctg {
+// sets with more buckets than 2^this are first shrunk by msm_reduce_chunk_kernel (CTG_REDUCE_CHUNK_LOG, default 19)
+inline int reduce_chunk_log() {
+  static int v = -1;
+  // measured on B200 (tools/r2u.sh): without the chunk step the first halving levels are wide enough to be throughput-bound by
+  // themselves -- G2 2^20 reduce 4.0 -> 3.3 ms, G1 2^22 1.6 -> 1.4 ms -- so the default only chunks sets above 2^19 buckets
+  if (v < 0) { const char* e = getenv("CTG_REDUCE_CHUNK_LOG"); v = e ? atoi(e) : 19; if (v < 10) v = 10; if (v > 20) v = 20; }
+  return v;
+}
 inline bool g2_pair_reduce() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("CTG_G2_PAIR"); v = !(e && *e == '0'); }
@@ -518,7 +526,8 @@ template <class F> struct MsmHost {
       ws.cap_part_bytes = pb;
     }
     // reduction scratch: chunk sums (2 * 2^16) + halving trees (main, weights, O_k: < 4 N points in all) per set
-    const size_t red_n = plan.nbuckets_per_set > 65536u ? 65536u : plan.nbuckets_per_set;
+    const size_t red_cap = (size_t)1 << reduce_chunk_log();
+    const size_t red_n = plan.nbuckets_per_set > red_cap ? red_cap : plan.nbuckets_per_set;
     const size_t cb = ((size_t)batch * plan.nsets * (6 * red_n + 64) + 256) * sizeof(XYZZ<F>);
     if (cb > ws.cap_chunk_bytes) {
       if (ws.chunk) cudaFree(ws.chunk);
@@ -656,9 +665,10 @@ template <class F> struct MsmHost {
       int shift = 0;
       const XYZZ<F>* wt_src = nullptr;
       uint32_t wt_count = 0;
-      if (N > (1u << 16)) {   // shrink to 2^16 items with chunked running sums
+      const uint32_t chunk_cap = 1u << reduce_chunk_log();
+      if (N > chunk_cap) {   // shrink to chunk_cap items with chunked running sums
         shift = 0;
-        while ((N >> shift) > (1u << 16)) shift++;
+        while ((N >> shift) > chunk_cap) shift++;
         const uint32_t T = N >> shift;
         XYZZ<F>* run = take(T);
         XYZZ<F>* wt = take(T);
@@ -707,6 +717,8 @@ template <class F> struct MsmHost {
         }
         if ((used + 64) * sizeof(XYZZ<F>) > ws.cap_chunk_bytes) return fail(ctx, CTG_ERR_STATE, "msm: reduction scratch too small");
         if constexpr (std::is_same<F, Fq2>::value) {
+          // every level, wide ones too: measured at 2^20 (2^19 buckets, no chunk step) 3.3 ms all-paired against 4.3 ms with one
+          // thread per addition on the levels above 16 K outputs (the 255-register single-thread kernel holds half the warps)
           if (g2_pair_reduce()) msm_halve_pair_kernel<0><<<dim3((2 * threads + 127) / 128, nsets), 128, 0, st>>>(args);
           else msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
         } else {
