@@ -13,6 +13,8 @@ void hm_fq_mul(const Fq* a, const Fq* b, Fq* o, uint64_t n) { for (uint64_t i = 
 void hm_fq_add(const Fq* a, const Fq* b, Fq* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i] + b[i]; }
 void hm_fq_sub(const Fq* a, const Fq* b, Fq* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i] - b[i]; }
 void hm_fq2_mul(const Fq2* a, const Fq2* b, Fq2* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i] * b[i]; }
+void hm_fr_sqr(const Fr* a, Fr* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].sqr(); }
+void hm_fq_sqr(const Fq* a, Fq* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].sqr(); }
 void hm_fq2_sqr(const Fq2* a, Fq2* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = a[i].sqr(); }
 // lazy-reduction sums of products: o = a*b + c*d, o = a*b - c*d (Fq), o = a*b - c*d (Fq2)
 void hm_fq_mul2_add(const Fq* a, const Fq* b, const Fq* c, const Fq* d, Fq* o, uint64_t n) { for (uint64_t i = 0; i < n; i++) o[i] = Fq::mul2_add(a[i], b[i], c[i], d[i]); }

@@ -61,6 +61,19 @@ def test_fr_mul_special_form_reduction_rows(hm):
     assert np.array_equal(out, ark.fr_mul(a, one))
 
 
+@pytest.mark.parametrize("field", ["fr", "fq"])
+def test_dedicated_squaring_equals_product(hm, field):
+    """Fp::sqr (the symmetric half of the partial products left out, rows multiplied by the limbs of 2a) against a * a from the
+    oracle: edge values, limbs drawn from {0, 1, 2^31, 2^32 - 1} (every carry of the doubling and of the skipped positions), random."""
+    mod, w = (B.R_MOD, 8) if field == "fr" else (B.P_MOD, 12)
+    limbs = [0, 1, 0x80000000, 0xFFFFFFFF, 0x7FFFFFFF]
+    vals = _edge(mod, 2000) + [sum(rnd.choice(limbs) << (32 * i) for i in range(w)) % mod for _ in range(3000)]
+    a = ark.ints_to_words(vals, w)
+    out = np.zeros_like(a)
+    getattr(hm, f"hm_{field}_sqr")(_p(a), _p(out), C.c_uint64(len(vals)))
+    assert np.array_equal(out, getattr(ark, f"{field}_mul")(a, a))
+
+
 def test_fr_mont_conversions(hm):
     vals = _edge(B.R_MOD, 50)
     a = ark.ints_to_words(vals, 8)

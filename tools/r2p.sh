@@ -1,6 +1,7 @@
 O=gpurun_out; T=r2p
 mkdir -p $O
 nvidia-smi -L > $O/${T}_smi.txt
+(time timeout 600 python -c "import __graft_entry__ as g; g.smoke()") > $O/${T}_smoke.log 2>&1; echo "smoke exit $?"; tail -2 $O/${T}_smoke.log
 (time timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 8 --steps 10 --warmup 3) > $O/${T}_bench_n8.json 2> $O/${T}_bench_n8.err; echo "bench n8 exit $?"; tail -5 $O/${T}_bench_n8.err
 python - <<'PY'
 import json
