@@ -29,7 +29,8 @@ for p in (ROOT, os.path.join(ROOT, "contangle-zkcp_b200")):
 import numpy as np  # noqa: E402
 
 MAC32_PER_G1_POINT = 48_000      # SURVEY 8(d) canonical schedule: 16 signed windows x (8M + 2S) x 300 MAC32 per Fq product (side field only)
-MAC32_PER_MADD_EXECUTED = 2_844  # what the kernel executes per mixed addition: 8 products x 300 + one 2-product lazy reduction (444)
+MAC32_PER_MADD_EXECUTED = 2_712  # what the kernel executes per mixed addition: 6 products x 300 + 2 dedicated squarings x 234 (66 of the 144 partial
+                                 # products left out) + one 2-product lazy reduction (444)
 OUT = sys.stdout
 BATCH_C_BITS = int(os.environ.get("CTG_BENCH_BATCH_C_BITS", "0"))   # window width of the keys of the batched rows (0 = the library's choice)
 METRIC = "g1_msm_throughput"
