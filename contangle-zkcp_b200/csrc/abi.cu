@@ -48,6 +48,7 @@ int32_t ensure_scratch(ctg_ctx* ctx, size_t bytes) {
   if (bytes <= ctx->scratch_bytes) return CTG_OK;
   if (ctx->scratch) {
     CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaMemset(ctx->scratch, 0, ctx->scratch_bytes);   // it held assignments, randomness or trapdoor powers
     cudaFree(ctx->scratch);
     ctx->scratch = nullptr;
     ctx->scratch_bytes = 0;
@@ -211,8 +212,8 @@ void ctg_ctx_destroy(ctg_ctx* ctx) {
   lanes_destroy(ctx);
   for (auto& w : ctx->ws) msm_ws_free(w);
   split_destroy(ctx);
-  if (ctx->scratch) cudaFree(ctx->scratch);
-  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->scratch) { cudaMemset(ctx->scratch, 0, ctx->scratch_bytes); cudaFree(ctx->scratch); }   // secrets do not outlive the context in HBM
+  if (ctx->pinned) { memset(ctx->pinned, 0, ctx->pinned_bytes); cudaFreeHost(ctx->pinned); }
   if (ctx->events_ready) for (auto& e : ctx->ev) cudaEventDestroy(e);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;

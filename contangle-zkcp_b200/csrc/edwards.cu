@@ -7,6 +7,9 @@
 // scalar's BigInteger bits; affine results are unique group elements, so any correct group law gives the same bytes.
 // Here: extended coordinates (X : Y : T : Z) with a = -1 (Hisil-Wong-Carter-Dawson: doubling 4M + 4S, mixed addition 7M + one
 // product by 2d; both complete because d is a non-square), 256 doublings, one binary-GCD inversion per result.
+// TIMING: like ark-ec's `mul`, both kernels are VARIABLE-TIME in the scalar (the plain kernel branches on each bit, the table
+// kernel skips zero digits and indexes its table by the digit): do not run them on a GPU shared with an adversary who can time
+// kernels.  Scratch that held scalars, assignments or trapdoor powers is zeroed before it is freed or handed back.
 // One thread per scalar; integer-pipe bound (about 3 100 Fr products per scalar, 96 bytes in and 64 out).  With one shared base
 // and thousands of scalars (bulk encrypt: G and pk) a window table replaces the doublings: <= 32 additions per scalar.
 #include <string>
@@ -165,6 +168,7 @@ int32_t ctg_te_mul_batch(ctg_ctx* ctx, const ctg_fr* d, const ctg_fr* points, ui
   memcpy(&dd, d, sizeof(Fr));
   CTG_TRY(te_mul_dev(ctx, dd, d_points, n_points == 1, d_scalars, n, d_out, ctx->stream));
   CTG_CUDA(ctx, cudaMemcpyAsync(out, d_out, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  CTG_CUDA(ctx, cudaMemsetAsync(d_scalars, 0, sb, ctx->stream));   // the scalars are secrets (sk of keygen, r of encrypt): not left in scratch
   CTG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return CTG_OK;
 }

@@ -429,7 +429,7 @@ void lanes_destroy(ctg_ctx* ctx) {
       if (!(idx == 0 && i == 0) && L.st[i]) cudaStreamDestroy(L.st[i]);
       msm_ws_free(L.ws[i]);
     }
-    if (L.scratch) cudaFree(L.scratch);
+    if (L.scratch) { cudaMemset(L.scratch, 0, L.scratch_bytes); cudaFree(L.scratch); }   // the assignment z and (r, s) lived here
     if (L.st_hi) { cudaStreamSynchronize(L.st_hi); cudaStreamDestroy(L.st_hi); }
     cudaEventDestroy(L.ev_zfull); cudaEventDestroy(L.ev_wm);
     cudaEventDestroy(L.ev_z);
@@ -445,6 +445,7 @@ int32_t lane_scratch(ctg_ctx* ctx, ProveLane& L, size_t bytes) {
   if (L.scratch) {
     for (int i = 0; i < 5; i++) CTG_CUDA(ctx, cudaStreamSynchronize(L.st[i]));
     CTG_CUDA(ctx, cudaStreamSynchronize(L.st_hi));
+    cudaMemset(L.scratch, 0, L.scratch_bytes);
     cudaFree(L.scratch);
     L.scratch = nullptr; L.scratch_bytes = 0;
   }

@@ -333,7 +333,9 @@ int32_t ctg_poseidon_merkle_tree_dev(ctg_ctx* ctx, const ctg_poseidon* p, const 
  * Montgomery Fr images (ark_ed_on_bls12_381::EdwardsAffine field by field); scalars: 256-bit little-endian integers, 8 words
  * each (the scalar field's into_repr(); any 256-bit value is accepted); d: Montgomery.  The identity is (0, 1).
  * n_points must be 1 (one shared base) or n.  The ElGamal pad is then ctg_poseidon_hash_batch over the p_r pairs with k = 2 and
- * c2 = pad + m (ctg_field_op_batch).  Points are not checked to be on the curve (arkworks does not check in mul either). */
+ * c2 = pad + m (ctg_field_op_batch).  Points are not checked to be on the curve (arkworks does not check in mul either).
+ * Timing: variable-time in the scalar, like ark-ec's `mul` (bit-dependent branches / digit-indexed table); the library zeroes
+ * the scratch that held the scalars before returning. */
 int32_t ctg_te_mul_batch(ctg_ctx* ctx, const ctg_fr* d, const ctg_fr* points, uint64_t n_points, const uint32_t* scalars, uint64_t n, ctg_fr* out);
 int32_t ctg_te_mul_batch_dev(ctg_ctx* ctx, const ctg_fr* d, const void* d_points, uint64_t n_points, const void* d_scalars, uint64_t n, void* d_out);
 
