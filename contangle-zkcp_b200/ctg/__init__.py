@@ -27,7 +27,7 @@ OP_PAIRED_MUL, OP_PAIRED_SQR, OP_PAIRED_MUL2SUB, OP_PAIRED_IS_ZERO = 4, 5, 6, 7 
 # every symbol include/ctg_groth16.h declares (checked by tests/test_abi_cpu.py)
 EXPORTS = [
     "ctg_ctx_create", "ctg_ctx_device_count", "ctg_ctx_destroy", "ctg_last_error", "ctg_ctx_set_stream", "ctg_ctx_set_ba_levels", "ctg_ctx_set_msm_split", "ctg_sync", "ctg_launch_count",
-    "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch",
+    "ctg_last_timings", "ctg_dev_alloc", "ctg_dev_free", "ctg_h2d", "ctg_d2h", "ctg_field_op_batch", "ctg_field_op_batch_noalloc",
     "ctg_fr_mul_batch", "ctg_fq_mul_batch", "ctg_imad_peak_probe", "ctg_ntt_fr", "ctg_ntt_fr_dev",
     "ctg_bases_upload_g1", "ctg_bases_upload_g2", "ctg_bases_progression_g1", "ctg_bases_progression_g2",
     "ctg_bases_download", "ctg_bases_free", "ctg_bases_len", "ctg_bases_plan", "ctg_msm_g1", "ctg_msm_g2", "ctg_msm_g1_dev",
@@ -195,6 +195,15 @@ class Context:
         a, b = _arr(a, w), _arr(b, w)
         out = np.empty_like(a)
         self._check(load().ctg_field_op_batch(self.h, field, op, _ptr(a), _ptr(b), _ptr(out), C.c_size_t(a.shape[0])))
+        return out
+
+    def field_op_noalloc(self, field, op, a, b):
+        """ctg_field_op_batch_noalloc: the same element-wise kernel staged in the library's fixed 3 MiB device array (no cudaMalloc);
+        raises CtgError beyond 32 768 Fr / 21 845 Fq / 10 922 Fq2 elements.  Calls that overlap on one GPU race on that array."""
+        w = {FIELD_FR: FR_W, FIELD_FQ: FQ_W, FIELD_FQ2: 2 * FQ_W}[field]
+        a, b = _arr(a, w), _arr(b, w)
+        out = np.empty_like(a)
+        self._check(load().ctg_field_op_batch_noalloc(self.h, field, op, _ptr(a), _ptr(b), _ptr(out), C.c_size_t(a.shape[0])))
         return out
 
     def fr_mul(self, a, b):

@@ -68,6 +68,8 @@ extern "C" {
     pub fn ctg_sync(ctx: *mut ctg_ctx) -> i32;
     pub fn ctg_launch_count(ctx: *mut ctg_ctx) -> u64;
     pub fn ctg_last_timings(ctx: *mut ctg_ctx, out: *mut ctg_timings) -> i32;
+    /// No counterpart in the reference: ctg_field_op_batch without any allocation, staged in a fixed 3 MiB device array.
+    pub fn ctg_field_op_batch_noalloc(ctx: *mut ctg_ctx, field: c_int, op: c_int, a: *const c_void, b: *const c_void, out: *mut c_void, n: usize) -> i32;
     pub fn ctg_ntt_fr(ctx: *mut ctg_ctx, host_data: *mut ctg_fr, log_n: u32, inverse: c_int, coset: c_int) -> i32;
     pub fn ctg_bases_upload_g1(ctx: *mut ctg_ctx, pts: *const ctg_g1_affine, n: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_bases) -> i32;
     pub fn ctg_bases_upload_g2(ctx: *mut ctg_ctx, pts: *const ctg_g2_affine, n: u64, copies: c_int, c_bits: c_int, out: *mut *mut ctg_bases) -> i32;

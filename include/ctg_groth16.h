@@ -159,6 +159,15 @@ int32_t ctg_host_free(ctg_ctx* ctx, void* h_ptr);
 #define CTG_OP_PAIRED_IS_ZERO 7
 /* out[i] = a[i] (op) b[i]; host buffers of n elements (32 / 48 / 96 bytes each) */
 int32_t ctg_field_op_batch(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n);
+/* ctg_field_op_batch for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO counterpart in the reference.  Same arguments and results as
+ * ctg_field_op_batch (host buffers; op = CTG_OP_MUL / ADD / SUB only), but operands and result are staged in a fixed 3 MiB
+ * file-scope device array instead of the context's growable scratch, and the call performs no cudaMalloc / cudaFree:
+ *   limit   3 * n * element_bytes <= 3 MiB, i.e. n <= 32 768 (Fr), 21 845 (Fq), 10 922 (Fq2); beyond it CTG_ERR_INVALID, no fallback
+ *   cost    3 MiB of HBM on every GPU that loads the library, until the process exits
+ *   sharing every call on a device uses the SAME array, which keeps the previous call's contents (the result region is cleared at
+ *           the start of each call): calls that overlap on one GPU -- two contexts, two streams, two threads -- race; serialise them */
+int32_t ctg_field_op_batch_noalloc(ctg_ctx* ctx, int field, int op, const void* a, const void* b, void* out, size_t n);
 int32_t ctg_fr_mul_batch(ctg_ctx* ctx, const ctg_fr* a, const ctg_fr* b, ctg_fr* out, size_t n);
 int32_t ctg_fq_mul_batch(ctg_ctx* ctx, const ctg_fq* a, const ctg_fq* b, ctg_fq* out, size_t n);
 /* Measured integer-pipe peaks of this GPU: IMAD (32-bit) instructions/s over all SMs, and the
