@@ -373,9 +373,13 @@ inline int reduce_chunk_log() {
   if (v < 0) { const char* e = getenv("CTG_REDUCE_CHUNK_LOG"); v = e ? atoi(e) : 19; if (v < 10) v = 10; if (v > 20) v = 20; }
   return v;
 }
-inline bool g2_pair_reduce() {
+template <class F> struct PairOpsOf;
+template <> struct PairOpsOf<Fq> { typedef G1PairOps type; };
+template <> struct PairOpsOf<Fq2> { typedef G2PairOps type; };
+// CTG_G1_PAIR=0 / CTG_G2_PAIR=0 fall back to one thread per group operation (A/B runs)
+template <class F> inline bool pair_reduce() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("CTG_G2_PAIR"); v = !(e && *e == '0'); }
+  if (v < 0) { const char* e = getenv(std::is_same<F, Fq2>::value ? "CTG_G2_PAIR" : "CTG_G1_PAIR"); v = !(e && *e == '0'); }
   return v != 0;
 }
 
@@ -716,24 +720,16 @@ template <class F> struct MsmHost {
           }
         }
         if ((used + 64) * sizeof(XYZZ<F>) > ws.cap_chunk_bytes) return fail(ctx, CTG_ERR_STATE, "msm: reduction scratch too small");
-        if constexpr (std::is_same<F, Fq2>::value) {
-          // every level, wide ones too: measured at 2^20 (2^19 buckets, no chunk step) 3.3 ms all-paired against 4.3 ms with one
-          // thread per addition on the levels above 16 K outputs (the 255-register single-thread kernel holds half the warps)
-          if (g2_pair_reduce()) msm_halve_pair_kernel<0><<<dim3((2 * threads + 127) / 128, nsets), 128, 0, st>>>(args);
-          else msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
-        } else {
-          msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
-        }
+        // lane pairs on every level, wide ones too: measured for G2 at 2^20 (2^19 buckets, no chunk step) 3.3 ms all-paired against
+        // 4.3 ms with one thread per addition on the levels above 16 K outputs (the 255-register single-thread kernel holds half the warps)
+        if (pair_reduce<F>()) msm_halve_pair_kernel<typename PairOpsOf<F>::type><<<dim3((2 * threads + 127) / 128, nsets), 128, 0, st>>>(args);
+        else msm_halve_kernel<F><<<dim3((threads + 63) / 64, nsets), 64, 0, st>>>(args);
         CTG_KERNEL_CHECK(ctx);
         trees.swap(next);
       }
       XYZZ<F>* set_out = plan.nsets == 1 ? d_out : take(1);
-      if constexpr (std::is_same<F, Fq2>::value) {
-        if (g2_pair_reduce()) msm_reduce_final_pair_kernel<0><<<nsets, 64, 0, st>>>(finals, nslots, 2, shift, set_out);
-        else msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
-      } else {
-        msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
-      }
+      if (pair_reduce<F>()) msm_reduce_final_pair_kernel<typename PairOpsOf<F>::type><<<nsets, 64, 0, st>>>(finals, nslots, 2, shift, set_out);
+      else msm_reduce_final_kernel<F><<<nsets, 32, 0, st>>>(finals, nslots, 2, shift, set_out);
       CTG_KERNEL_CHECK(ctx);
       if (plan.nsets > 1) {
         msm_horner_kernel<F><<<(batch + 31) / 32, 32, 0, st>>>(set_out, plan.nsets, plan.c, d_out, batch);
