@@ -368,7 +368,7 @@ namespace ctg {
 // sets with more buckets than 2^this are first shrunk by msm_reduce_chunk_kernel (CTG_REDUCE_CHUNK_LOG, default 19)
 inline int reduce_chunk_log() {
   static int v = -1;
-  // measured on B200 (tools/r2u.sh): without the chunk step the first halving levels are wide enough to be throughput-bound by
+  // measured on B200 (tools/round2/r2u.sh): without the chunk step the first halving levels are wide enough to be throughput-bound by
   // themselves -- G2 2^20 reduce 4.0 -> 3.3 ms, G1 2^22 1.6 -> 1.4 ms -- so the default only chunks sets above 2^19 buckets
   if (v < 0) { const char* e = getenv("CTG_REDUCE_CHUNK_LOG"); v = e ? atoi(e) : 19; if (v < 10) v = 10; if (v > 20) v = 20; }
   return v;
