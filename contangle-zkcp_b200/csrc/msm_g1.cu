@@ -1,5 +1,7 @@
 // G1 instantiation of the MSM pipeline (see msm.cuh) + plan selection.
 #include <algorithm>
+#include <cstdlib>
+#include <cmath>
 
 #include "msm.cuh"
 
@@ -43,7 +45,24 @@ MsmPlan msm_make_plan(uint64_t n, int copies_wanted, int c_override, size_t poin
       red = 0.003 * nb;
       lat *= 0.1;
     }
-    double cost = 0.0004 * p.nwin * (double)nn + red + lat;
+    // Buckets cut by slice boundaries (msm_fixup_*): the sorted entry list is cut into slices of 16 entries (at most 296 x 128 of
+    // them), so a bucket holding q slices is stitched from q partial sums by ONE thread (q <= 8) or one warp (q / 32 serial additions
+    // per lane + a 5-level tree), at the latency of a lone group addition (~30 us G1, ~165 us G2).  Narrow windows on small inputs make
+    // q huge: MulChain 2^12 chose c = 4 (16 buckets of 16 K entries each) and spent 6 of its 8.2 ms there.  Measured on B200 with and
+    // without this term (tools/round2/r2z2.sh, r2z3.sh): proof 2^12 8.2 -> 3.0 ms, 2^8 1.9 ms; with queries of 8.3 K points the PoE-shaped
+    // proof over a 2^13 domain gains (3.67 -> 3.30 ms) and the one over a 2^14 domain loses as much (3.74 -> 4.12 ms), and MulChain 2^14
+    // loses (4.97 -> 5.5 ms: the term over-estimates the warp kernel there) -- so it only applies below 2^13 points, where it is a pure
+    // win.  Not for the batch twin, whose window was measured directly.  CTG_PLAN_FIXUP_TERM=0 turns it off.
+    double fix = 0.0;
+    static int use_fix = -1;
+    if (use_fix < 0) { const char* e = getenv("CTG_PLAN_FIXUP_TERM"); use_fix = !(e && *e == '0'); }
+    if (!batch_throughput && use_fix && nn < 8192) {
+      const double t_add = point_bytes > sizeof(G1Affine) ? 165.0 : 30.0;
+      const double slices = std::min(296.0 * 128.0, std::max(1.0, (double)nn * p.nwin / 16.0));
+      const double q = slices / nb;
+      fix = t_add * (q <= 1.0 ? 1.0 : (q <= 8.0 ? q : std::ceil(q / 32.0) + 5.0));
+    }
+    double cost = 0.0004 * p.nwin * (double)nn + red + lat + fix;
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = p; }
   }
   return best;

@@ -500,6 +500,46 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   cudaStream_t sw = L.st_hi;   // witness map + H MSM
   int ne = 0;
   auto mark = [&](cudaStream_t st) { if (timed && ne < 16) cudaEventRecord(L.ev_t[ne], st); ne++; };
+  // An alternative schedule, OFF by default: the witness map first, alone, and all five MSMs behind it (CTG_WM_FIRST_MAX_LOG = largest
+  // log2 domain it applies to).  Idea: beside four MSMs' long-lived CTAs the short witness-map kernels wait for SM slots however high
+  // their stream priority (2^16: 3.2 ms instead of < 1 ms alone).  Measured on B200 it loses all the same -- 2^12 8.2 -> 8.5 ms, 2^16
+  // 5.9 -> 6.3 ms, 2^18 14.3 -> 14.4 ms, 2^20 44.5 -> 44.0 ms: the critical path of a small proof is the G2 MSM, which then starts later.
+  static int wm_first_max_log = -1;
+  if (wm_first_max_log < 0) { const char* e = getenv("CTG_WM_FIRST_MAX_LOG"); wm_first_max_log = e ? atoi(e) : 0; }
+  const bool wm_first = phase == 0 && !host_partials_out && pk->shard_count == 1 && r->log_n <= wm_first_max_log;
+  // assignment-only MSMs on their own streams
+  struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
+  const Job jobs[4] = {{1, &pk->l, d_z + pk->ni + pk->l_lo, pk->l_cnt, 2},
+                       {2, &pk->a_ext, d_z + pk->ext_lo, pk->ext_cnt, 0},
+                       {3, &pk->b1_ext, d_z + pk->ext_lo, pk->ext_cnt, 1},
+                       {4, &pk->b2_ext, d_z + pk->ext_lo, pk->ext_cnt, -1}};
+  // Queue order = L, A, B1, B2.  (Queueing the G2 MSM first on a raised-priority stream, so that its latency-bound tail runs under
+  // the G1 accumulate kernels, was measured: 2^16 7.8 -> 7.5 ms, but 2^22 154 -> 159 ms and the fused batch 2 045 -> 1 441 proofs/s:
+  // the G2 kernels then delay the sorts of the other MSMs.  Timing events keep their slots: 2 + 2 * index in `jobs`.)
+  const int order[4] = {0, 1, 2, 3};
+  auto enqueue_jobs = [&](cudaEvent_t gate) -> int32_t {
+  for (int oi = 0; oi < 4; oi++) {
+    const Job& j = jobs[order[oi]];
+    ne = 2 + 2 * order[oi];
+    cudaStream_t st = L.st[j.stream];
+    CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
+    if (gate) CTG_CUDA(ctx, cudaStreamWaitEvent(st, gate, 0));
+    mark(st);                                                                 // 2,4,6,8
+    if (j.g1_slot >= 0) {
+      // A and B1 multiply the same scalars under the same plan: B1 reuses A's sorted entry list (one digit sort fewer per proof)
+      const MsmWorkspace* sorted = nullptr;
+      if (j.stream == 3 && j.cnt > 0 && same_plan(pk->a_ext, pk->b1_ext)) { sorted = &L.ws[2]; CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ws[2].ev_sorted, 0)); }
+      CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr, 1, 0, sorted));
+    } else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
+    mark(st);                                                                 // 3,5,7,9
+    if (early_mul && !host_partials_out && (j.g1_slot == 0 || j.g1_slot == 1)) {   // s * A / r * B1 under the remaining MSMs
+      scalar_mul_g1_kernel<<<1, 32, 0, st>>>(d_g1 + j.g1_slot, j.g1_slot == 0 ? s_m : r_m, B.d_early + j.g1_slot);
+      CTG_KERNEL_CHECK(ctx);
+    }
+    CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
+  }
+  return CTG_OK;
+  };
   if (phase != 2) {
   mark(s0);                                                                   // 0
   // Upload order: first the part of z this key's A/B1/B2/L MSMs read (for a point-range shard, 1/N of it), so that they start
@@ -521,35 +561,7 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   }
   CTG_CUDA(ctx, cudaEventRecord(L.ev_zfull, s0));
   mark(s0);                                                                   // 1
-  // assignment-only MSMs on their own streams
-  struct Job { int stream; const Bases* b; const Fr* sc; uint64_t cnt; int g1_slot; };
-  const Job jobs[4] = {{1, &pk->l, d_z + pk->ni + pk->l_lo, pk->l_cnt, 2},
-                       {2, &pk->a_ext, d_z + pk->ext_lo, pk->ext_cnt, 0},
-                       {3, &pk->b1_ext, d_z + pk->ext_lo, pk->ext_cnt, 1},
-                       {4, &pk->b2_ext, d_z + pk->ext_lo, pk->ext_cnt, -1}};
-  // Queue order = L, A, B1, B2.  (Queueing the G2 MSM first on a raised-priority stream, so that its latency-bound tail runs under
-  // the G1 accumulate kernels, was measured: 2^16 7.8 -> 7.5 ms, but 2^22 154 -> 159 ms and the fused batch 2 045 -> 1 441 proofs/s:
-  // the G2 kernels then delay the sorts of the other MSMs.  Timing events keep their slots: 2 + 2 * index in `jobs`.)
-  const int order[4] = {0, 1, 2, 3};
-  for (int oi = 0; oi < 4; oi++) {
-    const Job& j = jobs[order[oi]];
-    ne = 2 + 2 * order[oi];
-    cudaStream_t st = L.st[j.stream];
-    CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ev_z, 0));
-    mark(st);                                                                 // 2,4,6,8
-    if (j.g1_slot >= 0) {
-      // A and B1 multiply the same scalars under the same plan: B1 reuses A's sorted entry list (one digit sort fewer per proof)
-      const MsmWorkspace* sorted = nullptr;
-      if (j.stream == 3 && j.cnt > 0 && same_plan(pk->a_ext, pk->b1_ext)) { sorted = &L.ws[2]; CTG_CUDA(ctx, cudaStreamWaitEvent(st, L.ws[2].ev_sorted, 0)); }
-      CTG_TRY(msm_g1_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g1 + j.g1_slot, st, nullptr, 1, 0, sorted));
-    } else CTG_TRY(msm_g2_run(ctx, L.ws[j.stream], *j.b, (const uint32_t*)j.sc, j.cnt, true, d_g2, st, nullptr));
-    mark(st);                                                                 // 3,5,7,9
-    if (early_mul && !host_partials_out && (j.g1_slot == 0 || j.g1_slot == 1)) {   // s * A / r * B1 under the remaining MSMs
-      scalar_mul_g1_kernel<<<1, 32, 0, st>>>(d_g1 + j.g1_slot, j.g1_slot == 0 ? s_m : r_m, B.d_early + j.g1_slot);
-      CTG_KERNEL_CHECK(ctx);
-    }
-    CTG_CUDA(ctx, cudaEventRecord(L.ev_done[j.stream], st));
-  }
+  if (!wm_first) CTG_TRY(enqueue_jobs(nullptr));
   ne = 10;
   // witness map on the lane's main stream: the coset evaluations of a, b, c (the chains this rank owns) ...
   if (phase != 1 || chain_mask != 0) {   // tables are built (and synchronised) before any chain is enqueued
@@ -574,6 +586,11 @@ static int32_t prove_enqueue(ctg_ctx* ctx, int lane_idx, const ctg_pk* pk, const
   set_h_tail_kernel<<<1, 32, 0, sw>>>(d_abc, n, r_m, s_m);
   CTG_KERNEL_CHECK(ctx);
   mark(sw);                                                                   // 10
+  if (wm_first) {   // the four assignment MSMs start behind the witness map (see above); ev_t[15] is free of timing duty
+    CTG_CUDA(ctx, cudaEventRecord(L.ev_t[15], sw));
+    CTG_TRY(enqueue_jobs(L.ev_t[15]));
+    ne = 11;
+  }
   CTG_TRY(msm_g1_run(ctx, L.ws[0], pk->h_ext, (const uint32_t*)(d_abc + pk->h_lo), pk->h_cnt, true, d_g1 + 3, sw, nullptr));
   mark(sw);                                                                   // 11
   CTG_CUDA(ctx, cudaEventRecord(L.ev_wm, sw));

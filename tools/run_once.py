@@ -38,6 +38,16 @@ elif what == "prove":
     for _ in range(reps):
         _, tm = ctx.prove(dpk, dr, zm, r, s, timed=True)
         print(tm)
+elif what == "poe":            # lone PoE-shaped proofs (n_data = lg), generated key
+    r1cs, zm, _ = S.poe_shape(lg)
+    dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
+    dpk = dp.to_device_pk()
+    dp.free()
+    dr = ctx.upload_r1cs(r1cs)
+    r, s = S.fr_mont([0xABCDEF])[0], S.fr_mont([0x123457])[0]
+    for _ in range(reps):
+        _, tm = ctx.prove(dpk, dr, zm, r, s, timed=True)
+        print(tm)
 elif what == "batch":          # `lg` = proofs in the batch; PoE shape n_data = 1 (domain 2^13), generated key
     r1cs, zm, _ = S.poe_shape(1)
     dp = ctx.generate_parameters(r1cs, S.trapdoor()[0])
