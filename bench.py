@@ -656,17 +656,24 @@ def extras(ctx, torch, dev, stream, S, args):
     # ... and the reference's other production proof, PoPRP (SampleEntries): the REAL circuit (ctg/circuits.py) about a ciphertext
     # encrypted and Merkle-hashed on the device with the reference's own Poseidon table; 128 sampled entries of one 1024-leaf tree
     out["batched_poprp_1024_leaves"] = batched_row(ctx, S, None, 128, td_words, mac_peak, args.copies, poprp_leaves=1024)
+    # ... and the REAL Proof-of-Encryption circuit (EncryptCircuit restated gate by gate, ctg/circuits.py; 5 908 constraints at n = 1),
+    # about ciphertexts encrypted on the device: the key-encryption proof a seller makes per buyer request (lib/src/seller.rs:136-159)
+    out["batched_poe_real_1"] = batched_row(ctx, S, 1, 128, td_words, mac_peak, args.copies, poe_real=True)
     a, b = out["batched_poe_shape_1"], out["batched_poprp_1024_leaves"]
     out["batched_poe_plus_poprp"] = {"proofs": a["proofs"] + b["proofs"], "proofs_per_s": (a["proofs"] + b["proofs"]) / (a["proofs"] / a["proofs_per_s"] + b["proofs"] / b["proofs_per_s"]),
                                      "note": "two circuits, two device-resident keys, one ctg_prove_batch call each (key-encryption PoE + sampled-entry PoPRP: what a seller publishes per data set)"}
     return out
 
 
-def batched_row(ctx, S, n_data, nb, td_words, mac_peak, copies=0, seed=9, poprp_leaves=0):
+def batched_row(ctx, S, n_data, nb, td_words, mac_peak, copies=0, seed=9, poprp_leaves=0, poe_real=False):
     if poprp_leaves:
         import ctg
         from ctg import circuits
         r1cs, zb, _ = circuits.sample_entries_workload(ctx, ctg.poseidon_reference_params(), poprp_leaves, nb, seed=seed)
+    elif poe_real:
+        import ctg
+        from ctg import circuits
+        r1cs, zb, _ = circuits.encrypt_workload(ctx, ctg.poseidon_reference_params(), n_data, nb, seed=seed)
     else:
         r1cs, _, _ = S.poe_shape(n_data)
         zb = S.poe_shape_witnesses(ctx, n_data, nb, seed=seed)           # independent assignments, pageable host memory

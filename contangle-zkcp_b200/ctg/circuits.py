@@ -22,6 +22,9 @@ from .synthetic import R_MOD, fr_mont
 ONE = ("i", 0)
 JUBJUB_A = R_MOD - 1
 JUBJUB_D = (-10240 * pow(10241, -1, R_MOD)) % R_MOD
+JUBJUB_GEN = (8076246640662884909881801758704306714034609987455869804520522091855516602923,
+              13262374693698910701929044844600465831413122818447359594527400194675274060458)
+JUBJUB_ORDER = 6554484396890773809930967563523245729705921265872317281365359162392183254199
 
 
 class LC:
@@ -239,10 +242,70 @@ def sample_entries_circuit(pc, c1, leaf, leaf_sibling_hash, auth_path, leaf_inde
     return cs
 
 
+# ---- Proof of Encryption (EncryptCircuit, circuits-ark/src/encryption.rs:219-317) -----------------------------------------------------
+def _te_add_ints(p, q):
+    """The same affine group law on integers (constants of the fixed-base multiplication; witness-side arithmetic)."""
+    (x1, y1), (x2, y2) = p, q
+    t = JUBJUB_D * x1 % R_MOD * x2 % R_MOD * y1 % R_MOD * y2 % R_MOD
+    return ((x1 * y2 + y1 * x2) * pow(1 + t, -1, R_MOD) % R_MOD, (y1 * y2 + x1 * x2) * pow(1 - t, -1, R_MOD) % R_MOD)
+
+
+def te_add_const(cs, p, q_ints):
+    """p + Q for a CONSTANT point Q: the four cross products are linear in p, so 3 constraints (t, x3, y3) instead of 7."""
+    (x1, y1), (x2, y2) = p, q_ints
+    a, b, c, dd = cs.scale(x1, y2), cs.scale(y1, x2), cs.scale(x1, x2), cs.scale(y1, y2)
+    t = cs.mul(cs.scale(c, JUBJUB_D), dd)
+    num_x, num_y = cs.add(a, b), cs.add(dd, c)
+    den_x, den_y = cs.add(cs.const(1), t), cs.sub(cs.const(1), t)
+    x3 = cs.new_witness(num_x.v * pow(den_x.v, -1, R_MOD))
+    y3 = cs.new_witness(num_y.v * pow(den_y.v, -1, R_MOD))
+    cs.enforce(x3, den_x, num_x)
+    cs.enforce(y3, den_y, num_y)
+    return x3, y3
+
+
+def te_fixed_base_mul_le(cs, base_ints, bits):
+    """scalar_mul_le on a constant point (the generator, `CV::new_constant`, :228): the multiples 2^i G are constants."""
+    acc = (cs.const(0), cs.const(1))
+    base = base_ints
+    for i, bit in enumerate(bits):
+        s = te_add_const(cs, acc, base)
+        acc = (cs.select(bit, s[0], acc[0]), cs.select(bit, s[1], acc[1]))
+        if i + 1 < len(bits):
+            base = _te_add_ints(base, base)
+    return acc
+
+
+def encrypt_circuit(pc, pk, r, msg, c1, c2, n_slots=None, record=True, r_bits=256):
+    """EncryptCircuit::generate_constraints (:289-317) + verify_encryption (:219-262): plaintext slots as witnesses, then the
+    ciphertext as INPUT -- instance [1, c1.x, c1.y, c2[0 .. n)] -- then: the 256 bits of r, pk as a witness point, s = r pk,
+    c1' = r G, dh = sponge(s.x, s.y), c1' == c1, and per slot (dh + m_i - c2_i) * [c2_i != 0] = 0 with the is_zero pair.
+    pk, c1: (x, y) integers; r: integer; msg, c2: integers (slots beyond len(msg) are empty: zero plaintext, zero ciphertext)."""
+    n = len(c2) if n_slots is None else n_slots
+    assert len(msg) <= n and len(c2) <= n
+    cs = ConstraintSystem(record)
+    m_vars = [cs.new_witness(msg[i] if i < len(msg) else 0) for i in range(n)]              # :293-300
+    c1v = (cs.new_input(c1[0]), cs.new_input(c1[1]))                                          # ciphertext_var, Input mode (:264-287)
+    c2v = [cs.new_input(c2[i] if i < len(c2) else 0) for i in range(n)]
+    bits = [cs.boolean((r >> i) & 1) for i in range(r_bits)]                                  # :231-235
+    pkv = (cs.new_witness(pk[0]), cs.new_witness(pk[1]))                                      # :237
+    xx, yy = cs.mul(pkv[0], pkv[0]), cs.mul(pkv[1], pkv[1])                                   # on-curve check of the witness point
+    cs.enforce(cs.scale(xx, JUBJUB_D), yy, cs.sub(cs.sub(yy, xx), cs.const(1)))
+    s = te_scalar_mul_le(cs, pkv, bits)                                                       # :240
+    c1calc = te_fixed_base_mul_le(cs, JUBJUB_GEN, bits)                                       # :243
+    dh = poseidon_crh(cs, pc, [s[0], s[1]])                                                   # :245-249
+    cs.enforce_equal(c1calc[0], c1v[0])                                                       # :251
+    cs.enforce_equal(c1calc[1], c1v[1])
+    for mv, exp in zip(m_vars, c2v):                                                          # :253-262
+        z = cs.new_witness(1 if exp.v == 0 else 0)                                            # exp.is_zero()
+        inv = cs.new_witness(pow(exp.v, -1, R_MOD) if exp.v else 0)
+        cs.enforce(exp, inv, cs.sub(cs.const(1), z))
+        cs.enforce(exp, z, cs.zero())
+        cs.enforce(cs.sub(cs.add(dh, mv), exp), cs.sub(cs.const(1), z), cs.zero())            # conditional_enforce_equal
+    return cs
+
+
 # ---- the workload above the C ABI: encrypt -> Merkle tree -> sampled-entry statements ---------------------------------------
-JUBJUB_GEN = (8076246640662884909881801758704306714034609987455869804520522091855516602923,
-              13262374693698910701929044844600465831413122818447359594527400194675274060458)
-JUBJUB_ORDER = 6554484396890773809930967563523245729705921265872317281365359162392183254199
 
 
 def sample_entries_workload(ctx, poseidon_words, n_leaves, count, seed=1):
@@ -280,3 +343,37 @@ def sample_entries_workload(ctx, poseidon_words, n_leaves, count, seed=1):
     m = len(zs[0])
     z = fr_mont([v for row in zs for v in row]).reshape(count, m, 8)
     return r1cs, z, publics
+
+
+def encrypt_workload(ctx, poseidon_words, n_data, count, seed=1):
+    """What the seller does per buyer request / per block (lib/src/zk/encryption.rs:65-85): `count` independent hashed-ElGamal
+    encryptions of n_data byte-valued elements under one public key -- on the device (ctg_te_mul_batch + ctg_poseidon_hash_batch) --
+    and the Proof-of-Encryption statement of each.  Returns (r1cs, z (count, m, 8) Montgomery words, public inputs per proof
+    [c1.x, c1.y, c2...] as integers)."""
+    import random
+    from .synthetic import fr_from_mont_words, ints_to_words
+    rnd = random.Random(seed)
+    pc = PoseidonConstants.from_words(*poseidon_words)
+    pos = ctx.poseidon(*poseidon_words)
+    sk = rnd.randrange(1, JUBJUB_ORDER)
+    d_w, gen_w = fr_mont([JUBJUB_D])[0], fr_mont(list(JUBJUB_GEN))
+    pk_w = ctx.te_mul_batch(d_w, gen_w.reshape(1, 2, 8), ints_to_words([sk], 8))[0]
+    pk = tuple(fr_from_mont_words(pk_w))
+    rs = [rnd.randrange(1, JUBJUB_ORDER) for _ in range(count)]
+    msgs = [[rnd.randrange(1, 256) for _ in range(n_data)] for _ in range(count)]
+    c1_w, c2_w = ctx.elgamal_encrypt_batch(pos, d_w, gen_w, pk_w, ints_to_words(rs, 8), fr_mont([v for m in msgs for v in m]).reshape(count, n_data, 8))
+    pos.free()
+    c1s = fr_from_mont_words(c1_w.reshape(-1, 8))
+    c2s = fr_from_mont_words(c2_w.reshape(-1, 8))
+    r1cs, zs, publics = None, [], []
+    for k in range(count):
+        c1 = (c1s[2 * k], c1s[2 * k + 1])
+        c2 = c2s[k * n_data:(k + 1) * n_data]
+        cs = encrypt_circuit(pc, pk, rs[k], msgs[k], c1, c2, record=r1cs is None)
+        if r1cs is None:
+            r1cs = cs.r1cs()
+        zs.append(cs.assignment())
+        publics.append([c1[0], c1[1]] + list(c2))
+    z = fr_mont([v for row in zs for v in row]).reshape(count, len(zs[0]), 8)
+    return r1cs, z, publics
+

@@ -79,6 +79,61 @@ def test_sample_entries_circuit_rejects_false_statements():
         assert not _satisfied(cs.r1cs(), cs.assignment()), kw
 
 
+@pytest.mark.parametrize("n_msg,n_slots", [(1, 1), (3, 5)])
+def test_encrypt_circuit_is_satisfied_sized_and_rejects(n_msg, n_slots):
+    """The reference's Proof-of-Encryption circuit (EncryptCircuit, circuits-ark/src/encryption.rs:219-317) as built by ctg/circuits.py:
+    instance [1, c1.x, c1.y, c2[0..n)], satisfied by an honest encryption made with the big-int oracle (empty slots included), not by a
+    tampered ciphertext, another randomness or another plaintext."""
+    pc, params, _ = _reference_poseidon()
+    r = random.Random(50 + n_slots)
+    sk, rr = r.randrange(J.SUBGROUP_ORDER), r.randrange(J.SUBGROUP_ORDER)
+    pk = J.keygen(sk)
+    msgs = [r.randrange(1, 256) for _ in range(n_msg)]
+    c1, c2 = J.encrypt(params, pk, msgs, rr)
+    cs = CI.encrypt_circuit(pc, pk, rr, msgs, c1, c2, n_slots=n_slots)
+    r1cs, z = cs.r1cs(), cs.assignment()
+    assert r1cs["num_instance"] == 3 + n_slots and z[:3 + n_msg] == [1, c1[0], c1[1]] + c2 and z[3 + n_msg:3 + n_slots] == [0] * (n_slots - n_msg)
+    # 256 bit checks, the on-curve check, a variable-base and a fixed-base scalar multiplication, one sponge, c1 == c1', 3 per slot
+    assert r1cs["num_constraints"] == 256 + 3 + (256 * 9 + 255 * 7) + 256 * 5 + 275 + 2 + 3 * n_slots
+    assert _satisfied(r1cs, z)
+    assert CI.encrypt_circuit(pc, pk, rr, msgs, c1, c2, n_slots=n_slots, record=False).assignment() == z
+    bad = list(c2)
+    bad[0] = (bad[0] + 1) % B.R_MOD
+    for kw in ({"c2": bad}, {"r": rr + 1}, {"msg": [msgs[0] + 1] + msgs[1:]}, {"c1": J.add(c1, J.GEN)}):
+        args = dict(pk=pk, r=rr, msg=msgs, c1=c1, c2=c2)
+        args.update(kw)
+        cs2 = CI.encrypt_circuit(pc, n_slots=n_slots, **args)
+        assert not _satisfied(cs2.r1cs(), cs2.assignment()), list(kw)
+
+
+@pytest.mark.gpu
+def test_encrypt_then_prove_encryption_on_gpu():
+    """BASELINE.json configs[0] with the reference's statement instead of a shape: encrypt on the device, prove the PoE circuit on the
+    device (one lone proof and a batch), verify with the big-int pairing check against the ciphertext as public input."""
+    _, params, words = _reference_poseidon()
+    ctx = ctg.Context(0)
+    r1cs, zb, publics = CI.encrypt_workload(ctx, words, 2, 3, seed=77)
+    assert S.domain_size(r1cs) == 8192 and r1cs["num_instance"] == 5
+    td_words, _ = S.trapdoor()
+    dp = ctx.generate_parameters(r1cs, td_words)
+    key = dp.download()
+    dpk = dp.to_device_pk()
+    dp.free()
+    dr = ctx.upload_r1cs(r1cs)
+    rs = ark.fr_mont_from_ints([rnd.randrange(B.R_MOD) for _ in range(6)]).reshape(3, 2, 8)
+    lone = ctx.prove(dpk, dr, zb[0], rs[0][0], rs[0][1])
+    assert all(np.array_equal(g, w) for g, w in zip(lone, ark.create_proof(key, r1cs, zb[0], rs[0][0], rs[0][1])))
+    out = ctx.prove_batch(dpk, dr, zb, rs)
+    assert np.array_equal(out[0], np.concatenate(lone))
+    for k in range(3):
+        pk_ = (out[k][:24], out[k][24:72], out[k][72:])
+        assert util.groth16_verify_words(key, pk_, publics[k])
+    wrong = list(publics[1])
+    wrong[3] = (wrong[3] + 1) % B.R_MOD                                                  # another ciphertext element
+    assert not util.groth16_verify_words(key, (out[1][:24], out[1][24:72], out[1][72:]), wrong)
+    dpk.free(); dr.free(); ctx.close()
+
+
 @pytest.mark.gpu
 def test_encrypt_merkle_path_prove_chain_on_gpu():
     pc, params, words = _reference_poseidon()
